@@ -1,0 +1,98 @@
+/* cno_b200.h -- C ABI of libcno_b200.so: the B200 (sm_100a) implementation of the CNO activation
+ * hot path (filtered_lrelu / upfirdn2d / bias_act / CIN).
+ *
+ * This is the drop-in boundary.  The reference crosses it with pybind11 torch
+ * extensions built by torch_utils/custom_ops.py:53 (get_plugin); each entry point below names the
+ * reference plugin function it replaces.  Differences by design:
+ *   - plain pointers + sizes, no torch types; the caller owns every buffer (the library never
+ *     allocates, frees or synchronises) and passes the CUDA stream explicitly;
+ *   - no global mutable state (the reference stages filters through one __constant__ buffer,
+ *     filtered_lrelu.cu:69-70), so calls are multi-stream and CUDA-graph safe;
+ *   - bf16 is a first-class dtype.
+ * Return value: 0 = ok, -1 = "no specialised kernel for these arguments" (the caller falls back to
+ * the generic composition exactly as filtered_lrelu.py:215-221 does), >0 = cudaError_t.
+ * All tensors are dense NCHW ("planes" = N*C images of H x W) unless stated otherwise.
+ */
+#ifndef CNO_B200_H
+#define CNO_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { CNO_F32 = 0, CNO_BF16 = 1, CNO_F16 = 2, CNO_F64 = 3 };
+enum { CNO_SIGN_NONE = 0, CNO_SIGN_WRITE = 1, CNO_SIGN_READ = 2 };
+
+int cno_version(void);
+/* last error text of the calling thread ("" if none) */
+const char* cno_last_error(void);
+
+/* replaces _plugin.bias_act(x, b, xref, yref, dy, grad, dim, act, alpha, gain, clamp)
+ * (bias_act.cpp:24-82, kernel bias_act.cu:15-139).  act = cuda_idx 1..9 of bias_act.py:13-23;
+ * grad 0: y = clamp(act(x+b)*gain); grad 1/2: first / second order gradient (x carries the incoming
+ * gradient).  Null pointers = "tensor not given".  bias index = (i / step_b) % size_b.
+ * clamp < 0 = no clamp. */
+int cno_bias_act(const void* x, const void* b, const void* xref, const void* yref, const void* dy,
+                 void* y, int dtype, int64_t numel, int64_t size_b, int64_t step_b, int grad,
+                 int act, float alpha, float gain, float clamp, void* stream);
+
+/* replaces _plugin.upfirdn2d(x, f, upx, upy, downx, downy, padx0, padx1, pady0, pady1, flip, gain)
+ * (upfirdn2d.cpp:8-90).  f: DEVICE pointer to fp32 taps, [fh, fw] row major; separable = 1 means f
+ * holds fw taps for the horizontal pass followed by fh taps for the vertical pass and both passes run
+ * in ONE kernel (the reference needs two launches, upfirdn2d.py:235-237).  Output size must be
+ * (in*up + pad0 + pad1 - f + down) / down (upfirdn2d.cpp:27-28). */
+int cno_upfirdn2d(const void* x, void* y, const float* f, int dtype, int separable,
+                  int64_t planes, int in_h, int in_w, int out_h, int out_w, int fw, int fh,
+                  int upx, int upy, int downx, int downy, int padx0, int pady0,
+                  int flip, float gain, void* stream);
+
+/* replaces _plugin.filtered_lrelu(x, fu, fd, b, si, up, down, px0, px1, py0, py1, sx, sy, gain, slope,
+ * clamp, flip_filter, write_signs) (filtered_lrelu.cpp:8-201): ONE fused kernel
+ * bias -> FIR upsample -> gain, leaky-ReLU, clamp, 2-bit sign mask write/read -> FIR downsample.
+ * fu / fd: HOST pointers to the separable fp32 taps (fu_taps, fd_taps entries).  b may be NULL.
+ * mask layout (filtered_lrelu.cpp:79-86): [planes, mask_h, mask_pitch] bytes, element x at byte
+ * x>>2 bits 2*(x&3); 1 = negative, 2 = clamped.  sign_mode READ uses offsets (sx, sy) and treats
+ * positions outside [0,mask_w) x [0,mask_h) as "pass" (filtered_lrelu.cu:680-687).
+ * db: optional fp32[C] accumulator (must be zeroed by the caller): receives sum of y over N,H,W
+ * (fuses `db = dx.sum([0,2,3])`, filtered_lrelu.py:257-258).  clamp < 0 or +inf = none. */
+int cno_filtered_lrelu(const void* x, void* y, const void* b, uint8_t* mask, float* db,
+                       const float* fu, const float* fd, int dtype,
+                       int n, int c, int in_h, int in_w, int out_h, int out_w,
+                       int fu_taps, int fd_taps, int up, int down, int px0, int py0,
+                       int mask_h, int mask_w, int mask_pitch, int sx, int sy, int sign_mode,
+                       float gain, float slope, float clamp, int flip, void* stream);
+
+/* supported-configuration probe for the fused kernel (mirrors filtered_lrelu.cpp:38-48):
+ * 0 = fused kernel available, -1 = use the generic composition. */
+int cno_filtered_lrelu_query(int dtype, int in_h, int in_w, int out_h, int out_w, int fu_taps,
+                             int fd_taps, int up, int down, int px0, int py0);
+
+/* replaces _plugin.filtered_lrelu_act_(x, si, sx, sy, gain, slope, clamp, write_signs)
+ * (filtered_lrelu.cpp:205-282, kernel filtered_lrelu.cu:1097-1203): in-place gain*lrelu, clamp on a
+ * dense [planes,h,w] tensor with 2-bit mask write / read.  Generic-fallback only. */
+int cno_filtered_lrelu_act(void* x, uint8_t* mask, int dtype, int64_t planes, int h, int w,
+                           int mask_h, int mask_w, int mask_pitch, int sx, int sy, int sign_mode,
+                           float gain, float slope, float clamp, void* stream);
+
+/* CIN = FILM.forward with instance norm (CNO_timeModule_CIN.py:60-70), one pass over x:
+ *   mu, rstd per plane; y = (x-mu)*rstd * (gamma[c]*scale[n,c]) + (beta[c]*scale[n,c] + shift[n,c]).
+ * gamma, beta fp32[C]; scale, shift fp32[N,C]; mean, rstd fp32[N,C] outputs (saved for backward). */
+int cno_cin_fwd(const void* x, void* y, const float* gamma, const float* beta, const float* scale,
+                const float* shift, float* mean, float* rstd, int dtype, int n, int c, int hw,
+                float eps, void* stream);
+/* backward: dx (same dtype as x) and per-plane fp32[N,C] reductions
+ *   s1 = sum(dy), s2 = sum(dy * xhat)   (dgamma = sum_n scale*s2, dbeta = sum_n scale*s1,
+ *   dscale = gamma*s2 + beta*s1, dshift = s1 -- finished by the host wrapper on [N,C] tensors). */
+int cno_cin_bwd(const void* x, const void* dy, void* dx, const float* gamma, const float* scale,
+                const float* mean, const float* rstd, float* s1, float* s2, int dtype, int n, int c,
+                int hw, void* stream);
+
+/* Measurement helper used by bench.py / tests (not part of the reference surface): FP32 FMA issue
+ * rate probe.  variant 0 = scalar FFMA, 1 = packed fma.rn.f32x2.  Writes elapsed-cycle-independent
+ * results to out[threads]; returns 0. */
+int cno_probe_fma(float* out, int variant, int blocks, int threads, int iters, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,321 @@
+// Core of the fused filtered_lrelu kernel, written so that the SAME source compiles
+//   - under nvcc as the device code of flrelu_fused.cu (registers + shared memory + FFMA2), and
+//   - under g++ as a sequential emulation used by tests/test_fused_emulation.py to check the index
+//     mathematics on the CPU (test infrastructure only; the product path is the CUDA kernel).
+//
+// Algorithm (new design, not the reference's tile scheme of filtered_lrelu.cu:131-1091):
+//   a thread owns FOUR adjacent columns of the up-sampled image (= one byte of the 2-bit sign mask)
+//   and streams down the rows of its plane:
+//     h-up   : polyphase horizontal up-FIR of the new input row from the TMA-staged x tile   (registers)
+//     v-up   : polyphase vertical up-FIR from a register window of the last 6-7 h-up rows     (registers)
+//     act    : gain (folded into the v-up taps), leaky ReLU, clamp, sign bits written / read  (registers)
+//     v-down : each activated row is scattered into 6 rotating output-row accumulators        (registers)
+//   finished rows go to shared memory once (D buffer), and a second phase applies the horizontal
+//   down-FIR and writes y with 16-byte stores.  Zero halo recompute horizontally, the 266x266
+//   intermediate of a 128x128 plane never leaves registers, all FIR arithmetic is packed
+//   fma.rn.f32x2 with taps coming from kernel-parameter (uniform) registers.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define FLR_DEV __device__ __forceinline__
+#define FLR_UNROLL _Pragma("unroll")
+#else
+#define FLR_DEV inline
+#define FLR_UNROLL
+#include <math.h>
+#include <string.h>
+#endif
+
+namespace flr {
+
+struct f2 { float x, y; };
+struct alignas(16) f4 { float x, y, z, w; };
+
+FLR_DEV f2 mk2(float a, float b) { f2 r; r.x = a; r.y = b; return r; }
+FLR_DEV float f4c(const f4& v, int c) { return c == 0 ? v.x : c == 1 ? v.y : c == 2 ? v.z : v.w; }
+
+// d = a * b + c on both lanes.  Device: one FFMA2 (ptxas folds broadcast operands to .F32 form).
+FLR_DEV f2 ffma2(f2 a, f2 b, f2 c) {
+#if defined(__CUDA_ARCH__)
+    f2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;"
+        : "=l"(*reinterpret_cast<unsigned long long*>(&d))
+        : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)),
+          "l"(*reinterpret_cast<unsigned long long*>(&c)));
+    return d;
+#else
+    return mk2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y));
+#endif
+}
+
+FLR_DEV uint32_t f_bits(float v) {
+#if defined(__CUDA_ARCH__)
+    return __float_as_uint(v);
+#else
+    uint32_t u; memcpy(&u, &v, 4); return u;
+#endif
+}
+
+enum { SIGN_NONE = 0, SIGN_WRITE = 1, SIGN_READ = 2 };
+
+// element -> fp32 (specialised for bf16 / fp16 by flrelu_fused.cu)
+template <class T> struct Cvt;
+template <> struct Cvt<float> { static FLR_DEV float get(float v) { return v; } };
+
+
+constexpr int NSTAGE = 3;
+
+// Everything the kernel needs besides the tensor map.  Filled by the host (flrelu_fused.cu).
+struct Params {
+    // tap tables first, 16-byte aligned, so that (lane0, lane1) pairs are aligned 64-bit operands
+    alignas(16) float hx[2][8][2];   // h-up taps  [phase pair][k][lane], zero padded, scaled by UP
+    alignas(16) float vy[4][8];      // v-up taps  [phase][k], scaled by UP * gain
+    alignas(16) float fd[32];        // down taps in correlation order
+    void* y; const void* b; uint8_t* mask; float* db;
+    int NC, C, H, W, UH, UW, OH, OW;
+    int G, P;                  // column groups per plane (ceil(UW/4)); planes per CTA
+    int nbands, BO;            // row bands per plane, output rows per band
+    int cminX, cminY;          // first input column / row offset of the polyphase windows
+    int bwx;                   // x tile row pitch (elements) = TMA box width
+    int dp;                    // D row pitch in floats (multiple of 32)
+    int ncq, ncq_shift;        // output column quads per row = ceil(OW/4); log2 when a power of two, else -1
+    int stage_bytes;           // bytes of one x stage (multiple of 128)
+    int mask_h, mask_w, mask_pitch, sx, sy;
+    float slope;
+};
+
+template <int UP_, int DOWN_, int RX_, int RY_>
+struct Cfg {
+    static constexpr int UP = UP_, DOWN = DOWN_, RX = RX_, RY = RY_;
+    static constexpr int NTU = 6, ND = 6;                    // taps per up phase, rows in flight per down FIR
+    static constexpr int TD = ND * DOWN;
+    static constexpr int WLX = NTU + (RX < UP - 1 ? 1 : 0);
+    static constexpr int WLY = NTU + (RY < UP - 1 ? 1 : 0);
+    static constexpr int NXS = WLX + (UP == 2 ? 1 : 0);      // x samples a thread reads per input row
+    static constexpr int PB = ND * DOWN;                     // up-res rows per body
+    static constexpr int PQ = PB / UP;                       // input rows per body
+    static constexpr int KO = ND;                            // output rows per body
+    static constexpr int M = (WLY - 1 + PQ - 1) / PQ;        // bodies per x stage
+    static constexpr int RS = M * PQ;                        // input rows per x stage (>= WLY-1)
+    static constexpr int NF4 = (DOWN * 3 + TD + 3) / 4;      // float4 loads per h-down task
+    static_assert(PB % UP == 0, "body must hold whole input rows");
+};
+
+// geometry of one CTA (uniform values)
+struct CtaGeom {
+    int plane0, o0, o1, j_b0, q_b0, row0 /* global input row of stage 0, row 0 */, nbodies, nstages_total;
+};
+
+template <class C>
+FLR_DEV CtaGeom cta_geom(const Params& p, int block) {
+    CtaGeom g;
+    const int pg = block / p.nbands, band = block % p.nbands;
+    g.plane0 = pg * p.P;
+    g.o0 = band * p.BO;
+    g.o1 = g.o0 + p.BO < p.OH ? g.o0 + p.BO : p.OH;
+    g.j_b0 = C::DOWN * g.o0;
+    g.q_b0 = g.j_b0 / C::UP;
+    g.row0 = g.q_b0 + p.cminY + (C::WLY - 1) - C::RS;
+    g.nbodies = (g.o1 - g.o0 + C::ND - 1 + C::KO - 1) / C::KO;
+    g.nstages_total = 1 + (g.nbodies + C::M - 1) / C::M;
+    return g;
+}
+
+FLR_DEV int swz(int f4idx) { return f4idx ^ ((f4idx >> 3) & 7); }
+
+// ------------------------------------------------------------------------------------------------
+// per-thread state of the streaming phase (lives in registers on the device)
+// ------------------------------------------------------------------------------------------------
+template <class T, class C, int MODE>
+struct Stream {
+    f2 win[C::WLY][2];      // h-up rows: window of the vertical up-FIR, two column pairs
+    f2 acc[C::ND][2];       // rotating output-row accumulators of the vertical down-FIR
+    f2 bE[2];               // bias times the horizontal edge profile of the up-FIR
+    int unit, g;            // plane slot in the CTA, column group
+    bool active;
+    uint32_t colmask;       // WRITE: valid-column bits; READ: valid mask-element bits
+    int rd_byte, rd_shift;  // READ: first mask byte of this thread, bit shift
+    uint8_t* mrow0;         // mask row 0 of this thread's plane (+ group byte for WRITE)
+
+    template <class LD>
+    FLR_DEV void init(const Params& p, const CtaGeom& cg, int tid, LD ld_bias) {
+        unit = tid / p.G; g = tid - unit * p.G;
+        const int plane = cg.plane0 + unit;
+        active = unit < p.P && plane < p.NC;
+        FLR_UNROLL for (int r = 0; r < C::ND; r++) { acc[r][0] = mk2(0.f, 0.f); acc[r][1] = mk2(0.f, 0.f); }
+        FLR_UNROLL for (int w = 0; w < C::WLY; w++) { win[w][0] = mk2(0.f, 0.f); win[w][1] = mk2(0.f, 0.f); }
+        bE[0] = bE[1] = mk2(0.f, 0.f);
+        colmask = 0; rd_byte = 0; rd_shift = 0; mrow0 = nullptr;
+        if (!active) return;
+        // bias edge profile: A = hup(x) + b * sum_k [column valid] * tap
+        const float bias = p.b ? ld_bias(plane % p.C) : 0.f;
+        FLR_UNROLL for (int pr = 0; pr < 2; pr++) {
+            const int qx = (C::UP == 2) ? 2 * g + pr : g;
+            const int hp = (C::UP == 2) ? 0 : pr;
+            float e0 = 0.f, e1 = 0.f;
+            FLR_UNROLL for (int k = 0; k < C::WLX; k++) {
+                const int col = qx + p.cminX + k;
+                if (col >= 0 && col < p.W) { e0 += p.hx[hp][k][0]; e1 += p.hx[hp][k][1]; }
+            }
+            bE[pr] = mk2(e0 * bias, e1 * bias);
+        }
+        if (MODE == SIGN_WRITE) {
+            FLR_UNROLL for (int m = 0; m < 4; m++) if (4 * g + m < p.UW) colmask |= 3u << (2 * m);
+            mrow0 = p.mask + (int64_t)plane * p.mask_h * p.mask_pitch + g;
+        } else if (MODE == SIGN_READ) {
+            const int e0 = 4 * g + p.sx;
+            const int fl = (e0 >= 0) ? e0 / 4 : -((-e0 + 3) / 4);
+            rd_byte = fl; rd_shift = 2 * (e0 - 4 * fl);
+            FLR_UNROLL for (int m = 0; m < 4; m++) { const int e = e0 + m; if (e >= 0 && e < p.mask_w) colmask |= 3u << (2 * m); }
+            mrow0 = p.mask + (int64_t)plane * p.mask_h * p.mask_pitch;
+        }
+    }
+
+    // horizontal polyphase up-FIR of one staged input row -> two column pairs
+    FLR_DEV void hup(const Params& p, const T* xrow /* tile row of this unit */, bool rowvalid, f2 out[2]) {
+        float xs[8];
+        const int xoff = (C::UP == 2) ? 2 * g : g;
+#if defined(__CUDA_ARCH__)
+        if (C::UP == 2 && sizeof(T) == 4) {          // 8-byte aligned: four LDS.64
+            FLR_UNROLL for (int w = 0; w < 4; w++) {
+                const float2 t = reinterpret_cast<const float2*>(xrow + xoff)[w];
+                xs[2 * w] = t.x; xs[2 * w + 1] = t.y;
+            }
+        } else
+#endif
+        { FLR_UNROLL for (int w = 0; w < C::NXS; w++) xs[w] = Cvt<T>::get(xrow[xoff + w]); }
+        FLR_UNROLL for (int pr = 0; pr < 2; pr++) {
+            f2 a = rowvalid ? bE[pr] : mk2(0.f, 0.f);
+            const int qo = (C::UP == 2) ? pr : 0;
+            const int hp = (C::UP == 2) ? 0 : pr;
+            FLR_UNROLL for (int k = 0; k < C::WLX; k++)
+                a = ffma2(mk2(xs[qo + k], xs[qo + k]), mk2(p.hx[hp][k][0], p.hx[hp][k][1]), a);
+            out[pr] = a;
+        }
+    }
+
+    FLR_DEV void push(const f2 a[2]) {
+        FLR_UNROLL for (int w = 0; w + 1 < C::WLY; w++) { win[w][0] = win[w + 1][0]; win[w][1] = win[w + 1][1]; }
+        win[C::WLY - 1][0] = a[0]; win[C::WLY - 1][1] = a[1];
+    }
+
+    // leaky ReLU with the sign bits of four columns written to / read from `code`.
+    // (clamp is not handled by the fused kernel: the host plan refuses it and the caller composes
+    //  the generic path, exactly like an unsupported filter shape.)
+    FLR_DEV void act(const Params& p, f2 v[2], uint32_t& code) {
+        if (MODE == SIGN_READ) {
+            float e[4] = {v[0].x, v[0].y, v[1].x, v[1].y};
+            FLR_UNROLL for (int m = 0; m < 4; m++) if (code & (1u << (2 * m))) e[m] *= p.slope;
+            if (code & 0xaau) {                     // "clamped" codes written by the generic forward path
+                FLR_UNROLL for (int m = 0; m < 4; m++) if (code & (2u << (2 * m))) e[m] = 0.f;
+            }
+            v[0] = mk2(e[0], e[1]); v[1] = mk2(e[2], e[3]);
+        } else {
+            if (MODE == SIGN_WRITE) {
+                const uint32_t u0 = f_bits(v[0].x), u1 = f_bits(v[0].y), u2 = f_bits(v[1].x), u3 = f_bits(v[1].y);
+                code = ((u0 >> 31) | ((u1 >> 29) & 4u) | ((u2 >> 27) & 16u) | ((u3 >> 25) & 64u)) & colmask;
+            }
+            // lrelu(v) = max(v, slope*v); the host plan only admits 0 <= slope <= 1
+            const f2 sl = mk2(p.slope, p.slope), z = mk2(0.f, 0.f);
+            const f2 s0 = ffma2(v[0], sl, z), s1 = ffma2(v[1], sl, z);
+            v[0] = mk2(fmaxf(v[0].x, s0.x), fmaxf(v[0].y, s0.y)); v[1] = mk2(fmaxf(v[1].x, s1.x), fmaxf(v[1].y, s1.y));
+        }
+    }
+
+    FLR_DEV uint32_t read_code(const Params& p, int j) const {
+        const int my = j + p.sy;
+        if (my < 0 || my >= p.mask_h) return 0u;
+        const uint8_t* r = mrow0 + (int64_t)my * p.mask_pitch;
+        uint32_t b0 = (rd_byte >= 0 && rd_byte < p.mask_pitch) ? r[rd_byte] : 0u;
+        uint32_t b1 = (rd_shift && rd_byte + 1 >= 0 && rd_byte + 1 < p.mask_pitch) ? r[rd_byte + 1] : 0u;
+        return (((b1 << 8) | b0) >> rd_shift) & 0xffu & colmask;
+    }
+
+    // One body: PQ input rows -> PB up-res rows -> KO finished rows of the vertical down-FIR.
+    //   xtile : this unit's rows of the current x stage, first row of the body
+    //   grow0 : global input row index of that first row
+    //   jb    : global up-res row index of the body's first row
+    //   Dbuf  : this unit's KO x dp floats of the D buffer being filled
+    FLR_DEV void body(const Params& p, const T* xtile, int grow0, int jb, float* Dbuf) {
+        FLR_UNROLL for (int jl = 0; jl < C::PB; jl++) {
+            const int phi = jl % C::UP, qq = jl / C::UP;
+            if (phi == 0) {
+                const int grow = grow0 + qq;
+                f2 a[2];
+                hup(p, xtile + qq * p.bwx, grow >= 0 && grow < p.H, a);
+                push(a);
+            }
+            const int j = jb + jl;
+            uint32_t code = 0;
+            if (MODE == SIGN_READ) code = read_code(p, j);
+            // vertical polyphase up-FIR (taps carry UP * gain)
+            f2 v[2] = {mk2(0.f, 0.f), mk2(0.f, 0.f)};
+            FLR_UNROLL for (int k = 0; k < C::NTU; k++) {
+                const f2 t = mk2(p.vy[phi][k], p.vy[phi][k]);
+                v[0] = ffma2(win[(phi > C::RY ? 1 : 0) + k][0], t, v[0]);
+                v[1] = ffma2(win[(phi > C::RY ? 1 : 0) + k][1], t, v[1]);
+            }
+            act(p, v, code);
+            if (MODE == SIGN_WRITE) { if (j < p.UH) mrow0[(int64_t)j * p.mask_pitch] = (uint8_t)code; }
+            // vertical down-FIR, scatter form: row r of this body completes at jl = DOWN*r + DOWN-1
+            FLR_UNROLL for (int r = 0; r < C::ND; r++) {
+                const int t = (jl <= C::DOWN * r + C::DOWN - 1) ? jl + C::DOWN * (C::ND - 1 - r) : jl - C::DOWN * (r + 1);
+                const f2 tt = mk2(p.fd[t], p.fd[t]);
+                acc[r][0] = ffma2(v[0], tt, acc[r][0]);
+                acc[r][1] = ffma2(v[1], tt, acc[r][1]);
+            }
+            if (jl % C::DOWN == C::DOWN - 1) {
+                const int r = jl / C::DOWN;
+                f4 o; o.x = acc[r][0].x; o.y = acc[r][0].y; o.z = acc[r][1].x; o.w = acc[r][1].y;
+                reinterpret_cast<f4*>(Dbuf + r * p.dp)[swz(g)] = o;
+                acc[r][0] = mk2(0.f, 0.f); acc[r][1] = mk2(0.f, 0.f);
+            }
+        }
+    }
+
+    // warm-up: the WLY-1 rows that precede the first body (last rows of stage 0)
+    FLR_DEV void prologue(const Params& p, const T* xstage0_unit, int row0_global) {
+        FLR_UNROLL for (int w = 0; w < C::WLY - 1; w++) {
+            const int sr = C::RS - (C::WLY - 1) + w;
+            const int grow = row0_global + sr;
+            f2 a[2];
+            hup(p, xstage0_unit + sr * p.bwx, grow >= 0 && grow < p.H, a);
+            push(a);
+        }
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// horizontal down-FIR of the finished rows of one body; writes y.  Called by every thread.
+// ------------------------------------------------------------------------------------------------
+template <class T, class C, class ST>
+FLR_DEV void hdown_phase(const Params& p, const CtaGeom& cg, int tid, int nthreads, int body_idx,
+                         const float* Dbuf /* [P][KO][dp] */, ST store4) {
+    const int o_base = cg.o0 - (C::ND - 1) + body_idx * C::KO;
+    const int ntask = p.P * C::KO * p.ncq;
+    for (int task = tid; task < ntask; task += nthreads) {
+        int cq, t2;
+        if (p.ncq_shift >= 0) { cq = task & (p.ncq - 1); t2 = task >> p.ncq_shift; }
+        else { t2 = task / p.ncq; cq = task - t2 * p.ncq; }
+        const int r = t2 % C::KO, u = t2 / C::KO;
+        const int o = o_base + r, plane = cg.plane0 + u;
+        if (o < cg.o0 || o >= cg.o1 || plane >= p.NC) continue;
+        const f4* drow = reinterpret_cast<const f4*>(Dbuf + (u * C::KO + r) * p.dp);
+        f4 d[C::NF4];
+        FLR_UNROLL for (int i = 0; i < C::NF4; i++) d[i] = drow[swz(C::DOWN * cq + i)];
+        float out[4];
+        FLR_UNROLL for (int i = 0; i < 4; i++) {
+            f2 a = mk2(0.f, 0.f);
+            FLR_UNROLL for (int m = 0; m < C::TD / 2; m++)
+                {
+                const int e = C::DOWN * i + 2 * m;     // even: both lanes sit in the same float4
+                a = ffma2(mk2(f4c(d[e >> 2], e & 3), f4c(d[e >> 2], (e & 3) + 1)), mk2(p.fd[2 * m], p.fd[2 * m + 1]), a);
+            }
+            out[i] = a.x + a.y;
+        }
+        store4(plane, o, 4 * cq, out);
+    }
+}
+
+}  // namespace flr

@@ -1,0 +1,162 @@
+// Fused filtered_lrelu for sm_100a: bias -> FIR upsample -> gain/leaky-ReLU/clamp (+2-bit sign mask
+// write or read) -> FIR downsample in ONE kernel.  Replaces the reference's filtered_lrelu_kernel
+// (filtered_lrelu.cu:131-1091), setup_filters_kernel (:79-100) and the constant-memory copy
+// (:103-109); the algorithm is described in flrelu_core.h.  This file adds the Blackwell plumbing:
+// a 3-D TMA tensor map over x[planes, H, W] whose out-of-bounds zero fill supplies the padding halo,
+// a 3-stage mbarrier ring of row strips, and the launch logic.
+#pragma once
+#include "common.cuh"
+#include "flrelu_host.h"
+#include <cuda.h>
+
+namespace flr {
+template <> struct Cvt<__nv_bfloat16> { static __device__ __forceinline__ float get(__nv_bfloat16 v) { return __bfloat162float(v); } };
+template <> struct Cvt<__half> { static __device__ __forceinline__ float get(__half v) { return __half2float(v); } };
+}
+
+namespace flr_impl {
+using namespace flr;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+
+template <class T> __device__ __forceinline__ void store_quad(T* dst, const float* o);
+template <> __device__ __forceinline__ void store_quad<float>(float* dst, const float* o) {
+    *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+}
+template <> __device__ __forceinline__ void store_quad<__nv_bfloat16>(__nv_bfloat16* dst, const float* o) {
+    __nv_bfloat162 a = __floats2bfloat162_rn(o[0], o[1]), b = __floats2bfloat162_rn(o[2], o[3]);
+    uint2 u; u.x = *reinterpret_cast<uint32_t*>(&a); u.y = *reinterpret_cast<uint32_t*>(&b);
+    *reinterpret_cast<uint2*>(dst) = u;
+}
+template <> __device__ __forceinline__ void store_quad<__half>(__half* dst, const float* o) {
+    __half2 a = __floats2half2_rn(o[0], o[1]), b = __floats2half2_rn(o[2], o[3]);
+    uint2 u; u.x = *reinterpret_cast<uint32_t*>(&a); u.y = *reinterpret_cast<uint32_t*>(&b);
+    *reinterpret_cast<uint2*>(dst) = u;
+}
+
+template <class T, class C, int MODE>
+__global__ void __launch_bounds__(256, 2)
+flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ Params p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t* xst = smem;
+    float* D = reinterpret_cast<float*>(smem + (size_t)NSTAGE * p.stage_bytes);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(D + (size_t)2 * p.P * C::KO * p.dp);
+    const int tid = threadIdx.x;
+    const CtaGeom cg = cta_geom<C>(p, blockIdx.x);
+    const uint32_t stage_tx = (uint32_t)(p.P * C::RS * p.bwx * (int)sizeof(T));
+
+    if (tid == 0) {
+        for (int i = 0; i < NSTAGE; i++) mbar_init(&bars[i], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+    int next_load = 0;
+    auto issue = [&](int s) {
+        const int slot = s % NSTAGE;
+        mbar_expect_tx(&bars[slot], stage_tx);
+        tma_load_3d(xst + (size_t)slot * p.stage_bytes, &tmap, &bars[slot], p.cminX, cg.row0 + s * C::RS, cg.plane0);
+    };
+    if (tid == 0) while (next_load < cg.nstages_total && next_load < NSTAGE) issue(next_load++);
+
+    Stream<T, C, MODE> st;
+    st.init(p, cg, tid, [&](int ch) { return Cvt<T>::get(reinterpret_cast<const T*>(p.b)[ch]); });
+
+    mbar_wait(&bars[0], 0);
+    if (st.active) st.prologue(p, reinterpret_cast<const T*>(xst) + (size_t)st.unit * C::RS * p.bwx, cg.row0);
+
+    const bool vec_ok = (p.OW & 3) == 0;
+    T* const yb = reinterpret_cast<T*>(p.y);
+    auto store4 = [&](int plane, int o, int ox, const float* out) {
+        T* dst = yb + ((size_t)plane * p.OH + o) * p.OW + ox;
+        if (vec_ok) store_quad<T>(dst, out);
+        else {
+#pragma unroll
+            for (int i = 0; i < 4; i++) if (ox + i < p.OW) dst[i] = from_f32<T>(out[i]);
+        }
+    };
+
+    for (int k = 0; k < cg.nbodies; k++) {
+        const int s = 1 + k / C::M, slot = s % NSTAGE, sub = k % C::M;
+        if (sub == 0) mbar_wait(&bars[slot], (uint32_t)((s / NSTAGE) & 1));
+        if (st.active)
+            st.body(p, reinterpret_cast<const T*>(xst + (size_t)slot * p.stage_bytes) + ((size_t)st.unit * C::RS + sub * C::PQ) * p.bwx,
+                    cg.row0 + s * C::RS + sub * C::PQ, cg.j_b0 + k * C::PB,
+                    D + ((size_t)(k & 1) * p.P + st.unit) * C::KO * p.dp);
+        __syncthreads();
+        if (tid == 0) {
+            const int consumed = 1 + (k + 1) / C::M;
+            while (next_load < cg.nstages_total && next_load < consumed + NSTAGE) issue(next_load++);
+        }
+        hdown_phase<T, C>(p, cg, tid, blockDim.x, k, D + (size_t)(k & 1) * p.P * C::KO * p.dp, store4);
+    }
+}
+
+// ---- driver entry point for tensor-map encoding (no -lcuda link dependency) ----------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+inline EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* ptr = nullptr; cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess && qres == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)ptr;
+    }
+    return fn;
+}
+
+template <class T, class C, int MODE>
+int launch_variant(const Plan& plan, const CUtensorMap& map, cudaStream_t st) {
+    auto kern = flr_fused_kernel<T, C, MODE>;
+    static size_t configured = 0;      // per instantiation
+    if (plan.smem_bytes > configured) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem_bytes);
+        if (e != cudaSuccess) { cno_set_error("filtered_lrelu: cannot reserve %zu bytes of shared memory: %s", plan.smem_bytes, cudaGetErrorString(e)); return (int)e; }
+        configured = plan.smem_bytes;
+    }
+    kern<<<plan.blocks, plan.threads, plan.smem_bytes, st>>>(map, plan.p);
+    CNO_LAUNCH_CHECK();
+    return 0;
+}
+
+template <class T, class C>
+int launch_mode(const Plan& plan, const CUtensorMap& map, int mode, cudaStream_t st) {
+    if (mode == CNO_SIGN_WRITE) return launch_variant<T, C, SIGN_WRITE>(plan, map, st);
+    if (mode == CNO_SIGN_READ) return launch_variant<T, C, SIGN_READ>(plan, map, st);
+    return launch_variant<T, C, SIGN_NONE>(plan, map, st);
+}
+
+template <class T>
+int launch_cfg(const Plan& plan, const CUtensorMap& map, int mode, cudaStream_t st) {
+#define V(U, D, R) if (plan.up == U && plan.down == D && plan.rx == R && plan.ry == R) return launch_mode<T, Cfg<U, D, R, R>>(plan, map, mode, st);
+#ifdef FLR_QUICK      // development builds: only the CNO "I" variant
+    V(2, 2, 1)
+#else
+    V(2, 2, 0) V(2, 2, 1) V(2, 4, 0) V(2, 4, 1) V(4, 2, 0) V(4, 2, 1) V(4, 2, 2) V(4, 2, 3)
+#endif
+#undef V
+    return -1;
+}
+
+}  // namespace flr_impl

@@ -1,0 +1,46 @@
+"""Attach the B200 kernels to an (unmodified) checkout of the reference's CNO_Experiments.
+
+    import pregenerating_pde_b200 as cno
+    cno.patch_reference('/path/to/CNO_Experiments')     # before or after importing the reference modules
+
+After this, `torch_utils.ops.{filtered_lrelu,upfirdn2d,bias_act}` resolve their `_plugin` through our
+loader (the reference's Python wrappers run unchanged on the C-ABI library) and `FILM.forward` is the
+fused CIN.  Parameter names / state_dict keys are untouched (SURVEY §5 checkpoint constraint)."""
+import importlib
+import sys
+
+from .torch_utils import custom_ops as _our_custom_ops
+from . import cin as _cin
+
+_saved = {}
+
+
+def patch_reference(cno_root=None, patch_film=True):
+    if cno_root is not None and cno_root not in sys.path:
+        sys.path.insert(0, cno_root)
+    ref_custom_ops = importlib.import_module('torch_utils.custom_ops')
+    if 'get_plugin' not in _saved:
+        _saved['get_plugin'] = ref_custom_ops.get_plugin
+    ref_custom_ops.get_plugin = _our_custom_ops.get_plugin
+    for name in ('bias_act', 'upfirdn2d', 'filtered_lrelu'):
+        mod = importlib.import_module(f'torch_utils.ops.{name}')
+        mod._plugin = None            # force re-resolution through the patched loader
+    if patch_film:
+        try:
+            film_mod = importlib.import_module('CNO_timeModule_CIN')
+        except Exception:             # model module not importable (missing lightning etc.): ops only
+            film_mod = None
+        if film_mod is not None:
+            if 'film_forward' not in _saved:
+                _saved['film_forward'] = film_mod.FILM.forward
+            film_mod.FILM.forward = _cin.film_forward
+    return True
+
+
+def unpatch_reference():
+    if 'get_plugin' in _saved:
+        importlib.import_module('torch_utils.custom_ops').get_plugin = _saved.pop('get_plugin')
+        for name in ('bias_act', 'upfirdn2d', 'filtered_lrelu'):
+            importlib.import_module(f'torch_utils.ops.{name}')._plugin = None
+    if 'film_forward' in _saved:
+        importlib.import_module('CNO_timeModule_CIN').FILM.forward = _saved.pop('film_forward')

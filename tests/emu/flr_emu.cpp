@@ -1,0 +1,74 @@
+// Sequential CPU emulation of the fused filtered_lrelu kernel: compiles the SAME core header the
+// CUDA kernel uses (pregenerating-pde_b200/csrc/flrelu_core.h) with g++, replaces TMA by a
+// zero-filling copy and the thread grid by loops.  Test infrastructure: validates the polyphase /
+// band / mask index mathematics without a GPU.  fp32 only.
+#include "../../pregenerating-pde_b200/csrc/flrelu_host.h"
+#include <vector>
+#include <stdio.h>
+
+using namespace flr;
+
+template <class C, int MODE>
+static void run(const Plan& plan, const float* x, float* y, const float* bias) {
+    const Params& p = plan.p;
+    const int nthreads = plan.threads;
+    std::vector<float> xst((size_t)NSTAGE * p.P * C::RS * p.bwx);
+    std::vector<float> D((size_t)2 * p.P * C::KO * p.dp, NAN);   // NaN: catches reads of unwritten cells
+    auto tma = [&](int slot, int row, int plane0) {
+        float* dst = xst.data() + (size_t)slot * p.P * C::RS * p.bwx;
+        for (int u = 0; u < p.P; u++) for (int r = 0; r < C::RS; r++) for (int cidx = 0; cidx < p.bwx; cidx++) {
+            const int pl = plane0 + u, gy = row + r, gx = p.cminX + cidx;
+            float v = 0.f;
+            if (pl < p.NC && gy >= 0 && gy < p.H && gx >= 0 && gx < p.W) v = x[((size_t)pl * p.H + gy) * p.W + gx];
+            dst[((size_t)u * C::RS + r) * p.bwx + cidx] = v;
+        }
+    };
+    auto store4 = [&](int plane, int o, int ox, const float* out) {
+        for (int i = 0; i < 4; i++) if (ox + i < p.OW) y[((size_t)plane * p.OH + o) * p.OW + ox + i] = out[i];
+    };
+    for (int blk = 0; blk < plan.blocks; blk++) {
+        const CtaGeom cg = cta_geom<C>(p, blk);
+        std::vector<Stream<float, C, MODE>> th(nthreads);
+        int next_load = 0;
+        auto issue = [&](int s) { tma(s % NSTAGE, cg.row0 + s * C::RS, cg.plane0); };
+        while (next_load < cg.nstages_total && next_load < NSTAGE) issue(next_load++);
+        for (int t = 0; t < nthreads; t++) {
+            th[t].init(p, cg, t, [&](int ch) { return bias[ch]; });
+            if (th[t].active) th[t].prologue(p, xst.data() + (size_t)th[t].unit * C::RS * p.bwx, cg.row0);
+        }
+        for (int k = 0; k < cg.nbodies; k++) {
+            const int s = 1 + k / C::M, slot = s % NSTAGE;
+            for (int t = 0; t < nthreads; t++) if (th[t].active)
+                th[t].body(p, xst.data() + (size_t)slot * p.P * C::RS * p.bwx + ((size_t)th[t].unit * C::RS + (k % C::M) * C::PQ) * p.bwx,
+                           cg.row0 + s * C::RS + (k % C::M) * C::PQ, cg.j_b0 + k * C::PB,
+                           D.data() + ((size_t)(k & 1) * p.P + th[t].unit) * C::KO * p.dp);
+            const int consumed = 1 + (k + 1) / C::M;
+            while (next_load < cg.nstages_total && next_load < consumed + NSTAGE) issue(next_load++);
+            for (int t = 0; t < nthreads; t++)
+                hdown_phase<float, C>(p, cg, t, nthreads, k, D.data() + (size_t)(k & 1) * p.P * C::KO * p.dp, store4);
+        }
+    }
+}
+
+template <class C>
+static void run_mode(const Plan& plan, int mode, const float* x, float* y, const float* b) {
+    if (mode == SIGN_WRITE) run<C, SIGN_WRITE>(plan, x, y, b);
+    else if (mode == SIGN_READ) run<C, SIGN_READ>(plan, x, y, b);
+    else run<C, SIGN_NONE>(plan, x, y, b);
+}
+
+extern "C" int flr_emulate(const float* x, float* y, const float* b, uint8_t* mask, int n, int c, int in_h, int in_w,
+                           int out_h, int out_w, const float* fu, int fu_taps, const float* fd, int fd_taps, int up,
+                           int down, int px0, int py0, int mask_h, int mask_w, int mask_pitch, int sx, int sy,
+                           int mode, float gain, float slope, float clamp, int flip, int bands, int* info) {
+    Plan plan;
+    if (make_plan(plan, 4, n, c, in_h, in_w, out_h, out_w, fu, fu_taps, fd, fd_taps, up, down, px0, py0, gain, slope,
+                  clamp, flip, bands) != 0) return -1;
+    plan.p.b = b; plan.p.mask = mask; plan.p.mask_h = mask_h; plan.p.mask_w = mask_w; plan.p.mask_pitch = mask_pitch;
+    plan.p.sx = sx; plan.p.sy = sy;
+    if (info) { info[0] = plan.p.P; info[1] = plan.threads; info[2] = plan.blocks; info[3] = plan.p.nbands; info[4] = (int)plan.smem_bytes; }
+#define V(U, D, R) if (plan.up == U && plan.down == D && plan.rx == R && plan.ry == R) { run_mode<Cfg<U, D, R, R>>(plan, mode, x, y, b); return 0; }
+    V(2, 2, 0) V(2, 2, 1) V(2, 4, 0) V(2, 4, 1) V(4, 2, 0) V(4, 2, 1) V(4, 2, 2) V(4, 2, 3)
+#undef V
+    return -1;
+}

@@ -1,0 +1,350 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Every op is called through the package's
+public API -> plugin layer -> C ABI of libcno_b200.so and compared with the CPU oracle on the same
+seeded inputs and with the committed golden vectors produced by the reference."""
+import math
+import numpy as np
+import pytest
+import torch
+
+from oracle import cno_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope='module')
+def cno():
+    import pregenerating_pde_b200 as pkg
+    assert torch.cuda.is_available()
+    pkg._lib.load()
+    return pkg
+
+
+T = lambda a: torch.from_numpy(np.asarray(a))
+DEV = 'cuda'
+
+
+def rel(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def fl_case(cno, x, b, dy, cfg, dtype=torch.float32, **kw):
+    """returns (y, dx, db, mask) from the CUDA path"""
+    fu, fd = cfg['fu'], cfg['fd']
+    xg = x.to(DEV, dtype).requires_grad_(True)
+    bg = b.to(DEV, dtype).requires_grad_(True)
+    F = cno.filtered_lrelu
+    y = F.filtered_lrelu(xg, None if fu is None else fu.to(DEV), None if fd is None else fd.to(DEV), bg, up=cfg['up'],
+                         down=cfg['down'], padding=cfg['padding'], impl='cuda', **kw)
+    mask = y.grad_fn.saved_tensors[2] if y.grad_fn is not None else None
+    dx, db = torch.autograd.grad(y, [xg, bg], dy.to(DEV, dtype))
+    return y, dx, db, mask
+
+
+FL_GOLDEN = ['I16', 'D16', 'U8', 'I32', 'D32', 'U16', 'I8']
+
+
+@pytest.mark.parametrize('name', FL_GOLDEN)
+def test_filtered_lrelu_golden(cno, golden, name):
+    g = golden['filtered_lrelu']
+    up, down, *pad = [int(v) for v in g[f'{name}.cfg']]
+    cfg = dict(fu=T(g[f'{name}.fu']), fd=T(g[f'{name}.fd']), up=up, down=down, padding=pad)
+    x, b, dy = T(g[f'{name}.x']), T(g[f'{name}.b']), T(g[f'{name}.dy'])
+    # this configuration must run on the fused kernel, not the generic composition
+    lib = cno._lib.load()
+    assert lib.cno_filtered_lrelu_query(0, x.shape[2], x.shape[3], dy.shape[2], dy.shape[3], len(cfg['fu']), len(cfg['fd']),
+                                        up, down, pad[0], pad[2]) == 0
+    y, dx, db, mask = fl_case(cno, x, b, dy, cfg)
+    assert rel(y, T(g[f'{name}.y'])) < 1e-5          # fp32 tolerance of BASELINE.json
+    assert rel(dx, T(g[f'{name}.dx'])) < 1e-5
+    assert rel(db, T(g[f'{name}.db'])) < 1e-5
+    # sign mask: bit-exact against the sign of the reference pre-activation over the active region
+    v = T(g[f'{name}.v'])
+    sh, swb, swv = O.sign_mask_shape(y.shape[2:], cfg['fd'], down)
+    assert tuple(mask.shape[2:]) == (sh, swb)
+    code = O.unpack_sign_mask(mask.cpu(), swv)
+    ref = O.sign_mask_from_preact(v, 0.2, math.sqrt(2), None, sh, swv)
+    bad = code != ref
+    assert int((bad & (v[:, :, :sh, :swv].abs() > 1e-5)).sum()) == 0
+    assert int(bad.sum()) == 0, f'{int(bad.sum())} sign mismatches at |v| ~ 0'
+
+
+SWEEP = [('I', 128, 128, 2, 5), ('D', 128, 64, 2, 3), ('U', 64, 128, 2, 3), ('I', 64, 64, 3, 9), ('D', 64, 32, 1, 8),
+         ('U', 32, 64, 2, 4), ('I', 32, 32, 2, 16), ('I', 16, 16, 2, 32), ('D', 16, 8, 2, 32), ('U', 8, 16, 2, 32),
+         ('I', 8, 8, 4, 64)]
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize('name,s_in,s_out,N,C', SWEEP)
+def test_filtered_lrelu_sweep(cno, name, s_in, s_out, N, C, dtype):
+    cfg = O.lrelu_config(s_in, s_out)
+    g = torch.Generator().manual_seed(s_in * 3 + s_out + C)
+    x = torch.randn(N, C, s_in, s_in, generator=g).to(dtype).float()      # values representable in `dtype`
+    b = torch.randn(C, generator=g).to(dtype).float()
+    dy = torch.randn(N, C, s_out, s_out, generator=g).to(dtype).float()
+    xr, br = x.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    y_ref = O.filtered_lrelu(xr, cfg['fu'], cfg['fd'], br, up=cfg['up'], down=cfg['down'], padding=cfg['padding'])
+    dx_ref, db_ref = torch.autograd.grad(y_ref, [xr, br], dy)
+    y, dx, db, mask = fl_case(cno, x, b, dy, cfg, dtype)
+    assert y.dtype == dtype and dx.dtype == dtype
+    tol = 1e-5 if dtype == torch.float32 else 2e-2          # BASELINE.json tolerances
+    assert rel(y, y_ref) < tol and rel(dx, dx_ref) < tol and rel(db, db_ref) < (tol if dtype == torch.float32 else 3e-2)
+    v = O.filtered_lrelu_preact(x, cfg['fu'], b, up=cfg['up'], padding=cfg['padding'])
+    sh, swb, swv = O.sign_mask_shape(y.shape[2:], cfg['fd'], cfg['down'])
+    bad = O.unpack_sign_mask(mask.cpu(), swv) != O.sign_mask_from_preact(v, 0.2, math.sqrt(2), None, sh, swv)
+    assert int((bad & (v[:, :, :sh, :swv].abs() > 1e-5)).sum()) == 0
+    assert int(bad.sum()) <= 2
+
+
+def test_filtered_lrelu_generic_golden(cno, golden):
+    """clamp + flip + 8-tap filters: no fused variant -> generic composition on our kernels."""
+    g = golden['filtered_lrelu']
+    cfg = dict(fu=T(g['GEN.fu']), fd=T(g['GEN.fd']), up=2, down=2, padding=[5, 4, 6, 3])
+    y, dx, db, _ = fl_case(cno, T(g['GEN.x']), T(g['GEN.b']), T(g['GEN.dy']), cfg, gain=1.3, slope=0.1, clamp=0.7,
+                           flip_filter=True)
+    assert rel(y, T(g['GEN.y'])) < 1e-5 and rel(dx, T(g['GEN.dx'])) < 1e-5 and rel(db, T(g['GEN.db'])) < 1e-5
+
+
+@pytest.mark.parametrize('kw', [dict(up=1, down=1), dict(up=2, down=1), dict(up=1, down=2), dict(up=2, down=2, clamp=0.5),
+                                dict(up=2, down=2, slope=1.5), dict(up=2, down=2, f2d=True)])
+def test_filtered_lrelu_generic_paths(cno, kw):
+    kw = dict(kw)
+    f2d = kw.pop('f2d', False)
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(2, 3, 11, 9, generator=g); b = torch.randn(3, generator=g)
+    fu = torch.randn(4, 4, generator=g) if f2d else torch.randn(4, generator=g)
+    fd = torch.randn(3, 3, generator=g) if f2d else torch.randn(6, generator=g)
+    if kw['up'] == 1:
+        fu = None
+    if kw['down'] == 1:
+        fd = None
+    args = dict(padding=[4, 3, 5, 2], gain=1.1, **kw)
+    xr, br = x.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    y_ref = O.filtered_lrelu(xr, fu, fd, br, **args)
+    dy = torch.randn(y_ref.shape, generator=g)
+    dx_ref, db_ref = torch.autograd.grad(y_ref, [xr, br], dy)
+    cfg = dict(fu=fu, fd=fd, up=args.pop('up'), down=args.pop('down'), padding=args.pop('padding'))
+    y, dx, db, _ = fl_case(cno, x, b, dy, cfg, **args)
+    assert rel(y, y_ref) < 1e-5 and rel(dx, dx_ref) < 1e-5 and rel(db, db_ref) < 1e-5
+
+
+def test_filtered_lrelu_double_backward(cno):
+    cfg = O.lrelu_config(16, 16)
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(1, 2, 16, 16, generator=g); b = torch.randn(2, generator=g)
+    dy = torch.randn(1, 2, 16, 16, generator=g); ddx = torch.randn(1, 2, 16, 16, generator=g)
+
+    def run(fn, dev):
+        xx = x.to(dev).requires_grad_(True); bb = b.to(dev).requires_grad_(True); dd = dy.to(dev).requires_grad_(True)
+        y = fn(xx, cfg['fu'].to(dev), cfg['fd'].to(dev), bb)
+        dx, = torch.autograd.grad(y, [xx], dd, create_graph=True)
+        g_dy, = torch.autograd.grad(dx, [dd], ddx.to(dev))
+        return g_dy
+    ref = run(lambda xx, fu, fd, bb: O.filtered_lrelu(xx, fu, fd, bb, up=2, down=2, padding=cfg['padding']), 'cpu')
+    got = run(lambda xx, fu, fd, bb: cno.filtered_lrelu.filtered_lrelu(xx, fu, fd, bb, up=2, down=2, padding=cfg['padding']), DEV)
+    assert rel(got, ref) < 1e-5
+
+
+def test_filtered_lrelu_no_grad_and_bands(cno, monkeypatch):
+    """forward-only call writes no mask; full-size C1-shaped planes exercise the banded grid."""
+    cfg = O.lrelu_config(128, 128)
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(1, 2, 128, 128, generator=g); b = torch.randn(2, generator=g)
+    y_ref = O.filtered_lrelu(x, cfg['fu'], cfg['fd'], b, up=2, down=2, padding=cfg['padding'])
+    with torch.no_grad():
+        y = cno.filtered_lrelu.filtered_lrelu(x.to(DEV), cfg['fu'].to(DEV), cfg['fd'].to(DEV), b.to(DEV), up=2, down=2,
+                                              padding=cfg['padding'])
+    assert rel(y, y_ref) < 1e-5
+
+
+def test_filtered_lrelu_full_size_properties(cno):
+    """BASELINE config C1 [8,64,128,128]: size-independent checks (too slow for the CPU oracle in a test):
+    positive homogeneity, adjoint identity <dy, J dx> on the linearised op, and plane independence."""
+    cfg = O.lrelu_config(128, 128)
+    fu, fd = cfg['fu'].to(DEV), cfg['fd'].to(DEV)
+    F = lambda x, b: cno.filtered_lrelu.filtered_lrelu(x, fu, fd, b, up=2, down=2, padding=cfg['padding'])
+    g = torch.Generator(device=DEV).manual_seed(0)
+    x = torch.randn(8, 64, 128, 128, device=DEV, generator=g).requires_grad_(True)
+    b = torch.randn(64, device=DEV, generator=g).requires_grad_(True)
+    y = F(x, b)
+    assert y.shape == (8, 64, 128, 128) and torch.isfinite(y).all()
+    # lrelu is positively homogeneous and the filters are linear: F(2x, 2b) == 2 F(x, b)
+    assert rel(F(2 * x.detach(), 2 * b.detach()), 2 * y) < 1e-6
+    # y is piecewise linear in (x, b): y == J_x x + J_b b, so <dy, y> == <dx, x> + <db, b>
+    dy = torch.randn(y.shape, device=DEV, generator=g)
+    dx, db = torch.autograd.grad(y, [x, b], dy)
+    lhs = (dy.double() * y.double()).sum()
+    rhs = (dx.double() * x.double()).sum() + (db.double() * b.double()).sum()
+    assert abs(float(lhs - rhs)) / abs(float(lhs)) < 1e-5
+    # a plane's result does not depend on its neighbours in the batch
+    y1 = F(x.detach()[3:4, 10:11].contiguous(), b.detach()[10:11].contiguous())
+    assert torch.equal(y1, y.detach()[3:4, 10:11])
+    # spot-check 3 planes against the oracle
+    xs, bs = x.detach()[5:6, 20:23].cpu(), b.detach()[20:23].cpu()
+    y_ref = O.filtered_lrelu(xs, cfg['fu'], cfg['fd'], bs, up=2, down=2, padding=cfg['padding'])
+    assert rel(y[5:6, 20:23], y_ref) < 1e-5
+
+
+# ------------------------------------------------------------------------------------------------
+UP_SPECS = {'up2': dict(up=2, down=1, padding=[6, 5, 6, 5], gain=4),
+            'down2': dict(up=1, down=2, padding=[5, 5, 5, 5], gain=1),
+            'xy': dict(up=[2, 1], down=[1, 3], padding=[3, 2, 4, 1], gain=1.5, flip_filter=True),
+            'f2d': dict(up=2, down=2, padding=[2, 1, 0, 3], gain=1),
+            'crop': dict(up=1, down=1, padding=[-1, -2, 1, -1], gain=1)}
+
+
+@pytest.mark.parametrize('name', list(UP_SPECS))
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_upfirdn2d_golden(cno, golden, name, dtype):
+    g = golden['upfirdn2d']
+    x = T(g[f'{name}.x']).to(dtype)
+    xr = x.float().requires_grad_(True)
+    y_ref = O.upfirdn2d(xr, T(g[f'{name}.f']), **UP_SPECS[name])
+    dy = T(g[f'{name}.dy']).to(dtype)
+    dx_ref, = torch.autograd.grad(y_ref, [xr], dy.float())
+    xg = x.to(DEV).requires_grad_(True)
+    y = cno.upfirdn2d.upfirdn2d(xg, T(g[f'{name}.f']).to(DEV), **UP_SPECS[name])
+    dx, = torch.autograd.grad(y, [xg], dy.to(DEV))
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
+    assert y.shape == y_ref.shape
+    assert rel(y, y_ref) < tol and rel(dx, dx_ref) < tol
+    if dtype == torch.float32:
+        assert rel(y, T(g[f'{name}.y'])) < 1e-5 and rel(dx, T(g[f'{name}.dx'])) < 1e-5
+
+
+def test_upfirdn2d_helpers_and_identity(cno):
+    U = cno.upfirdn2d
+    x = torch.randn(2, 3, 32, 32)
+    assert torch.equal(U.upfirdn2d(x.to(DEV), None).cpu(), x)
+    f = U.setup_filter([1, 3, 3, 1, 1, 3, 3, 1])
+    for fn, kw in [(U.upsample2d, dict(up=2)), (U.downsample2d, dict(down=2)), (U.filter2d, {})]:
+        a = fn(x.to(DEV), f.to(DEV), **kw)
+        r = fn(x, f, impl='ref', **kw)
+        assert a.shape == r.shape and rel(a, r) < 1e-5
+
+
+@pytest.mark.parametrize('shape,f_taps,kw', [((32, 64, 128, 128), 12, dict(up=2, padding=[6, 5, 6, 5], gain=4)),
+                                             ((32, 64, 128, 128), 12, dict(down=2, padding=[5, 5, 5, 5]))])
+def test_upfirdn2d_full_size_adjoint(cno, shape, f_taps, kw):
+    """sweep-size planes: <y, dy> == <x, dx> (the backward is the adjoint op, upfirdn2d.py:248-258)."""
+    f = O.design_lowpass_filter(f_taps, 64 / 2.0001, 2 * (0.8 * 64 - 64 / 2.0001), 256).to(DEV)
+    x = torch.randn(*shape, device=DEV).requires_grad_(True)
+    y = cno.upfirdn2d.upfirdn2d(x, f, **kw)
+    dy = torch.randn_like(y)
+    dx, = torch.autograd.grad(y, [x], dy)
+    lhs, rhs = (y.double() * dy.double()).sum(), (x.double() * dx.double()).sum()
+    assert abs(float(lhs - rhs)) / abs(float(lhs)) < 1e-5
+    ref = O.upfirdn2d(x.detach()[:1, :2].cpu(), f.cpu(), **kw)
+    assert rel(y[:1, :2], ref) < 1e-5
+
+
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('act', list(O.ACTIVATIONS))
+def test_bias_act_golden(cno, golden, act):
+    g = golden['bias_act']
+    for tag, kw in [('def', {}), ('arg', dict(alpha=0.3, gain=1.7, clamp=0.9))]:
+        x = T(g['x']).to(DEV).requires_grad_(True); b = T(g['b']).to(DEV).requires_grad_(True)
+        y = cno.bias_act.bias_act(x, b, act=act, **kw)
+        dx, db = torch.autograd.grad(y, [x, b], T(g['dy']).to(DEV))
+        assert rel(y, T(g[f'{act}.{tag}.y'])) < 1e-5
+        assert rel(dx, T(g[f'{act}.{tag}.dx'])) < 1e-5
+        assert rel(db, T(g[f'{act}.{tag}.db'])) < 1e-5
+
+
+@pytest.mark.parametrize('act', ['tanh', 'sigmoid', 'elu', 'selu', 'softplus', 'swish', 'lrelu'])
+def test_bias_act_second_order_fp64(cno, act):
+    x = torch.randn(2, 4, 3, 8, dtype=torch.float64); b = torch.randn(4, dtype=torch.float64)
+    dy = torch.randn_like(x); ddx = torch.randn_like(x)
+
+    def run(fn, dev):
+        xx = x.to(dev).requires_grad_(True); bb = b.to(dev).requires_grad_(True); dd = dy.to(dev).requires_grad_(True)
+        y = fn(xx, bb)
+        dx, = torch.autograd.grad(y, [xx], dd, create_graph=True)
+        outs = torch.autograd.grad(dx, [xx, dd], ddx.to(dev), allow_unused=True)
+        return [o for o in outs if o is not None]
+    ref = run(lambda a, c: O.bias_act(a, c, act=act), 'cpu')
+    got = run(lambda a, c: cno.bias_act.bias_act(a, c, act=act), DEV)
+    assert len(ref) == len(got)
+    for r, q in zip(ref, got):
+        assert rel(q, r) < 1e-9
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16, torch.float16])
+def test_bias_act_dtypes_layouts(cno, dtype):
+    x = torch.randn(4, 8, 16, 16).to(dtype); b = torch.randn(8).to(dtype)
+    ref = O.bias_act(x.float(), b.float(), act='lrelu')
+    tol = 1e-6 if dtype == torch.float32 else 2e-2
+    assert rel(cno.bias_act.bias_act(x.to(DEV), b.to(DEV), act='lrelu'), ref) < tol
+    xc = x.to(DEV).contiguous(memory_format=torch.channels_last)
+    yc = cno.bias_act.bias_act(xc, b.to(DEV), act='lrelu')
+    assert yc.is_contiguous(memory_format=torch.channels_last) and rel(yc, ref) < tol
+    # odd element count (tail path) and dim=0 / rank-2
+    x2 = torch.randn(7, 13).to(dtype); b2 = torch.randn(7).to(dtype)
+    assert rel(cno.bias_act.bias_act(x2.to(DEV), b2.to(DEV), dim=0, act='relu'), O.bias_act(x2.float(), b2.float(), dim=0, act='relu')) < tol
+
+
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('name', ['c4s16', 'c6s8'])
+def test_cin_golden(cno, golden, name):
+    g = golden['cin']
+    w = {k[len(name) + 3:]: T(g[k]).to(DEV).requires_grad_(True) for k in g.files if k.startswith(name + '.p.')}
+
+    class M(torch.nn.Module):   # a FILM-shaped module without the reference import
+        pass
+    m = M()
+    C = w['norm.weight'].shape[0]
+    m.norm = torch.nn.InstanceNorm2d(C, affine=True).to(DEV)
+    m.inp2lat_sacale = torch.nn.Linear(1, 128).to(DEV); m.lat2scale = torch.nn.Linear(128, C).to(DEV)
+    m.inp2lat_bias = torch.nn.Linear(1, 128).to(DEV); m.lat2bias = torch.nn.Linear(128, C).to(DEV)
+    m.load_state_dict({k: v.detach() for k, v in w.items()})
+    x = T(g[f'{name}.x']).to(DEV).requires_grad_(True)
+    y = cno.cin.film_forward(m, x, T(g[f'{name}.t']).to(DEV))
+    names = [n for n, _ in m.named_parameters()]
+    grads = torch.autograd.grad(y, [x] + list(m.parameters()), T(g[f'{name}.dy']).to(DEV))
+    assert rel(y, T(g[f'{name}.y'])) < 1e-5
+    assert rel(grads[0], T(g[f'{name}.dx'])) < 2e-5
+    for n, gr in zip(names, grads[1:]):
+        assert rel(gr, T(g[f'{name}.g.{n}'])) < 5e-5, n
+
+
+@pytest.mark.parametrize('N,C,S', [(32, 16, 128), (8, 32, 64), (4, 64, 32), (4, 128, 16), (4, 256, 8), (1, 2, 256), (2, 3, 10)])
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_cin_sizes(cno, N, C, S, dtype):
+    g = torch.Generator().manual_seed(S + C)
+    x = (torch.randn(N, C, S, S, generator=g) * 1.5 + 0.3).to(dtype)
+    gamma, beta = torch.randn(C, generator=g), torch.randn(C, generator=g)
+    scale, shift = torch.randn(N, C, generator=g), torch.randn(N, C, generator=g)
+    dy = torch.randn(N, C, S, S, generator=g).to(dtype)
+    leaves = [t.clone().requires_grad_(True) for t in (x.float(), gamma, beta, scale, shift)]
+    y_ref = O.cin(*leaves)
+    g_ref = torch.autograd.grad(y_ref, leaves, dy.float())
+    dl = [x.to(DEV).requires_grad_(True)] + [t.to(DEV).requires_grad_(True) for t in (gamma, beta, scale, shift)]
+    y = cno.cin.cin(*dl)
+    g_got = torch.autograd.grad(y, dl, dy.to(DEV))
+    tol = 2e-5 if dtype == torch.float32 else 2e-2
+    assert rel(y, y_ref) < tol
+    for a, r in zip(g_got, g_ref):
+        assert rel(a, r) < (1e-4 if dtype == torch.float32 else 3e-2)
+
+
+def test_plugin_layer_matches_reference_signatures(cno):
+    """the objects get_plugin returns accept the reference's positional plugin calls."""
+    P = cno.custom_ops.get_plugin
+    e = torch.empty([0])
+    x = torch.randn(2, 3, 8, 8, device=DEV); b = torch.randn(3, device=DEV)
+    y = P('bias_act_plugin').bias_act(x, b, e, e, e, 0, 1, 3, 0.2, math.sqrt(2), -1)
+    assert rel(y, O.bias_act(x.cpu(), b.cpu(), act='lrelu')) < 1e-6
+    f = torch.randn(3, 4, device=DEV)
+    y = P('upfirdn2d_plugin').upfirdn2d(x, f, 2, 2, 1, 1, 2, 1, 2, 1, False, 1.0)
+    assert rel(y, O.upfirdn2d(x.cpu(), f.cpu(), up=2, padding=[2, 1, 2, 1])) < 1e-5
+    cfg = O.lrelu_config(8, 8)
+    y, so, rc = P('filtered_lrelu_plugin').filtered_lrelu(x, cfg['fu'].to(DEV), cfg['fd'].to(DEV), b, e, 2, 2, 11, 10, 11, 10,
+                                                          0, 0, math.sqrt(2), 0.2, float('inf'), False, True)
+    assert rc == 0 and so.dtype == torch.uint8 and so.shape == (2, 3, 26, 8)
+    assert rel(y, O.filtered_lrelu(x.cpu(), cfg['fu'], cfg['fd'], b.cpu(), up=2, down=2, padding=cfg['padding'])) < 1e-5
+    y2, so2, rc2 = P('filtered_lrelu_plugin').filtered_lrelu(x, torch.randn(4, device=DEV), cfg['fd'].to(DEV), b, e, 2, 2, 3, 3,
+                                                             3, 3, 0, 0, 1.0, 0.2, float('inf'), False, False)
+    assert rc2 == -1
+    with pytest.raises(RuntimeError):
+        P('filtered_lrelu_plugin').filtered_lrelu(x, cfg['fu'].to(DEV), cfg['fd'].to(DEV), b[:2], e, 2, 2, 11, 10, 11, 10, 0, 0,
+                                                  1.0, 0.2, float('inf'), False, False)
