@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libcno_b200.so')
+LIB_PATH = os.environ.get('CNO_B200_LIB') or os.path.join(_HERE, 'libcno_b200.so')
 
 F32, BF16, F16, F64 = 0, 1, 2, 3
 SIGN_NONE, SIGN_WRITE, SIGN_READ = 0, 1, 2

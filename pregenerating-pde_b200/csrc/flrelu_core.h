@@ -37,7 +37,7 @@ FLR_DEV float f4c(const f4& v, int c) { return c == 0 ? v.x : c == 1 ? v.y : c =
 
 // d = a * b + c on both lanes.  Device: one FFMA2 (ptxas folds broadcast operands to .F32 form).
 FLR_DEV f2 ffma2(f2 a, f2 b, f2 c) {
-#if defined(__CUDA_ARCH__)
+#if defined(__CUDA_ARCH__) && !defined(FLR_NO_FFMA2)
     f2 d;
     asm("fma.rn.f32x2 %0, %1, %2, %3;"
         : "=l"(*reinterpret_cast<unsigned long long*>(&d))
@@ -77,12 +77,15 @@ struct Params {
     int G, P;                  // column groups per plane (ceil(UW/4)); planes per CTA
     int nbands, BO;            // row bands per plane, output rows per band
     int cminX, cminY;          // first input column / row offset of the polyphase windows
+    int tmaX, xshift;          // TMA start column = cminX rounded down to a 16-byte boundary (the hardware faults on an
+                               // unaligned innermost coordinate; measured, tools/probes/tma_probe.cu); xshift = cminX - tmaX
     int bwx;                   // x tile row pitch (elements) = TMA box width
     int dp;                    // D row pitch in floats (multiple of 32)
     int ncq, ncq_shift;        // output column quads per row = ceil(OW/4); log2 when a power of two, else -1
     int stage_bytes;           // bytes of one x stage (multiple of 128)
     int mask_h, mask_w, mask_pitch, sx, sy;
     float slope;
+    int dbg;                   // bring-up only: stop after stage `dbg` (0 = run normally)
 };
 
 template <int UP_, int DOWN_, int RX_, int RY_>
@@ -175,12 +178,16 @@ struct Stream {
     // horizontal polyphase up-FIR of one staged input row -> two column pairs
     FLR_DEV void hup(const Params& p, const T* xrow /* tile row of this unit */, bool rowvalid, f2 out[2]) {
         float xs[8];
-        const int xoff = (C::UP == 2) ? 2 * g : g;
+        const int xoff = ((C::UP == 2) ? 2 * g : g) + p.xshift;
 #if defined(__CUDA_ARCH__)
-        if (C::UP == 2 && sizeof(T) == 4) {          // 8-byte aligned: four LDS.64
-            FLR_UNROLL for (int w = 0; w < 4; w++) {
-                const float2 t = reinterpret_cast<const float2*>(xrow + xoff)[w];
-                xs[2 * w] = t.x; xs[2 * w + 1] = t.y;
+        if (C::UP == 2 && sizeof(T) == 4) {          // LDS.64 from the even column at or below xoff
+            const float2* src = reinterpret_cast<const float2*>(xrow + (xoff & ~1));
+            if (xoff & 1) {                          // uniform branch (xshift is a launch constant)
+                float t[10];
+                FLR_UNROLL for (int w = 0; w < 5; w++) { const float2 v = src[w]; t[2 * w] = v.x; t[2 * w + 1] = v.y; }
+                FLR_UNROLL for (int w = 0; w < 8; w++) xs[w] = t[w + 1];
+            } else {
+                FLR_UNROLL for (int w = 0; w < 4; w++) { const float2 v = src[w]; xs[2 * w] = v.x; xs[2 * w + 1] = v.y; }
             }
         } else
 #endif

@@ -50,6 +50,7 @@ extern "C" int cno_filtered_lrelu(const void* x, void* y, const void* b, uint8_t
     if (sign_mode == CNO_SIGN_WRITE)
         CNO_CHECK_ARG(mask_h >= p.UH && mask_pitch >= p.G, "filtered_lrelu: mask [%d rows x %d bytes] smaller than [%d x %d]", mask_h, mask_pitch, p.UH, p.G);
     p.y = y; p.b = b; p.mask = mask; p.db = nullptr;
+    { const char* d = getenv("CNO_FLR_DEBUG"); p.dbg = d ? atoi(d) : 0; }
     p.mask_h = mask_h; p.mask_w = mask_w; p.mask_pitch = mask_pitch; p.sx = sx; p.sy = sy;
 
     EncodeTiledFn enc = get_encode();

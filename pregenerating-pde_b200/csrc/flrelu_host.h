@@ -62,7 +62,9 @@ static inline int make_plan(Plan& plan, int elem_size, int n, int c, int in_h, i
     p.cminX = -floor_div_i(px0, up);
     p.cminY = -floor_div_i(py0, up);
     const int epv = 16 / elem_size;                                    // elements per 16 bytes
-    int bwx = (up == 2) ? 2 * p.G + 6 : p.G + 6;
+    p.tmaX = floor_div_i(p.cminX, epv) * epv;
+    p.xshift = p.cminX - p.tmaX;
+    int bwx = ((up == 2) ? 2 * p.G + 6 : p.G + 6) + p.xshift + 1;     // +1: the odd-xshift path reads one float2 further
     bwx = (bwx + epv - 1) / epv * epv;
     if (bwx > 256) return -1;                                          // TMA box limit
     p.bwx = bwx;

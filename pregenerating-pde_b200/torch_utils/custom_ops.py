@@ -25,6 +25,19 @@ def _stream(t):
     return ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
 
 
+def _dense(t):
+    """non-overlapping and dense in some dimension order (bias_act.cpp:41 has_same_layout / is_non_overlapping_and_dense)"""
+    if t.is_contiguous() or t.is_contiguous(memory_format=torch.channels_last if t.ndim == 4 else torch.contiguous_format):
+        return True
+    dims = sorted((d for d in range(t.ndim) if t.size(d) > 1), key=lambda d: t.stride(d))
+    expect = 1
+    for d in dims:
+        if t.stride(d) != expect:
+            return False
+        expect *= t.size(d)
+    return True
+
+
 _host_taps = {}
 
 
@@ -60,7 +73,7 @@ class _BiasActPlugin:
             raise RuntimeError('b must be a vector matching dimension `dim` of x')
         if x.numel() > 2 ** 31 - 1:
             raise RuntimeError('x is too large')
-        if not x.is_non_overlapping_and_dense():
+        if not _dense(x):
             raise RuntimeError('x must be non-overlapping and dense')
         if grad < 0:
             raise RuntimeError('grad must be non-negative')

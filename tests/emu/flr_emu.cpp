@@ -17,7 +17,7 @@ static void run(const Plan& plan, const float* x, float* y, const float* bias) {
     auto tma = [&](int slot, int row, int plane0) {
         float* dst = xst.data() + (size_t)slot * p.P * C::RS * p.bwx;
         for (int u = 0; u < p.P; u++) for (int r = 0; r < C::RS; r++) for (int cidx = 0; cidx < p.bwx; cidx++) {
-            const int pl = plane0 + u, gy = row + r, gx = p.cminX + cidx;
+            const int pl = plane0 + u, gy = row + r, gx = p.tmaX + cidx;
             float v = 0.f;
             if (pl < p.NC && gy >= 0 && gy < p.H && gx >= 0 && gx < p.W) v = x[((size_t)pl * p.H + gy) * p.W + gx];
             dst[((size_t)u * C::RS + r) * p.bwx + cidx] = v;
