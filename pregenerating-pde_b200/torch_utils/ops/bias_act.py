@@ -91,7 +91,10 @@ class _BiasAct(torch.autograd.Function):
         if act != 'linear' or gain != 1 or clamp >= 0 or b is not None:
             y = _plugin.bias_act(x, bb, _EMPTY, _EMPTY, _EMPTY, 0, dim, spec.cuda_idx, alpha, gain, clamp)
         keep_x = 'x' in spec.ref or spec.has_2nd_grad
-        ctx.save_for_backward(x if keep_x else _EMPTY, bb if keep_x else _EMPTY, y if 'y' in spec.ref else _EMPTY)
+        # 'linear' keeps nothing in the reference (ref=''), so its plugin gradient ignores clamp; the impl='ref'
+        # definition (the parity target) zeroes the gradient where y was clamped, so y is kept in that case
+        keep_y = 'y' in spec.ref or (clamp >= 0 and spec.ref == '')
+        ctx.save_for_backward(x if keep_x else _EMPTY, bb if keep_x else _EMPTY, y if keep_y else _EMPTY)
         return y
 
     @staticmethod

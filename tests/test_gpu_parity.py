@@ -93,7 +93,8 @@ def test_filtered_lrelu_sweep(cno, name, s_in, s_out, N, C, dtype):
     sh, swb, swv = O.sign_mask_shape(y.shape[2:], cfg['fd'], cfg['down'])
     bad = O.unpack_sign_mask(mask.cpu(), swv) != O.sign_mask_from_preact(v, 0.2, math.sqrt(2), None, sh, swv)
     assert int((bad & (v[:, :, :sh, :swv].abs() > 1e-5)).sum()) == 0
-    assert int(bad.sum()) <= 2
+    # at |v| <= 1e-5 the sign depends on the fp32 summation order; 16-bit inputs make such near-cancellations commoner
+    assert int(bad.sum()) <= (2 if dtype == torch.float32 else 16)
 
 
 def test_filtered_lrelu_generic_golden(cno, golden):
@@ -266,7 +267,8 @@ def test_bias_act_second_order_fp64(cno, act):
     got = run(lambda a, c: cno.bias_act.bias_act(a, c, act=act), DEV)
     assert len(ref) == len(got)
     for r, q in zip(ref, got):
-        assert rel(q, r) < 1e-9
+        # alpha / gain cross the plugin boundary as C floats (bias_act.cpp:24), so gain = sqrt(2) carries 1.7e-8
+        assert rel(q, r) < (1e-7 if act in ('lrelu', 'swish') else 1e-9)
 
 
 @pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16, torch.float16])
