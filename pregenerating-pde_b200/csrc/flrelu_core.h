@@ -75,7 +75,7 @@ struct Params {
     void* y; const void* b; uint8_t* mask; float* db;
     int NC, C, H, W, UH, UW, OH, OW;
     int G, P;                  // column groups per plane (ceil(UW/4)); planes per CTA
-    int nbands, BO;            // row bands per plane, output rows per band
+    int ncta, rows_total;      // persistent CTAs; rows_total = plane groups * OH ("global row space", see cta_rows)
     int cminX, cminY;          // first input column / row offset of the polyphase windows
     int tmaX, xshift;          // TMA start column = cminX rounded down to a 16-byte boundary (the hardware faults on an
                                // unaligned innermost coordinate; measured, tools/probes/tma_probe.cu); xshift = cminX - tmaX
@@ -84,8 +84,8 @@ struct Params {
     int ncq, ncq_shift;        // output column quads per row = ceil(OW/4); log2 when a power of two, else -1
     int stage_bytes;           // bytes of one x stage (multiple of 128)
     int mask_h, mask_w, mask_pitch, sx, sy;
+    int mws, mnw, mstride;     // READ: staged mask window per row: first byte (multiple of 4, may be < 0), 32-bit words, smem row stride
     float slope;
-    int dbg;                   // bring-up only: stop after stage `dbg` (0 = run normally)
 };
 
 template <int UP_, int DOWN_, int RX_, int RY_>
@@ -102,21 +102,39 @@ struct Cfg {
     static constexpr int M = (WLY - 1 + PQ - 1) / PQ;        // bodies per x stage
     static constexpr int RS = M * PQ;                        // input rows per x stage (>= WLY-1)
     static constexpr int NF4 = (DOWN * 3 + TD + 3) / 4;      // float4 loads per h-down task
+    static constexpr int ALIGN = (DOWN % UP == 0) ? 1 : UP / DOWN;   // a segment must start on a whole input row
+    static constexpr int SNAP = 2 * KO;
     static_assert(PB % UP == 0, "body must hold whole input rows");
 };
 
-// geometry of one CTA (uniform values)
+// Work partition.  The output rows of all plane groups form one global row space
+//   gr = plane_group * OH + o,   0 <= gr < rows_total,
+// cut into `ncta` nearly equal contiguous ranges, one per persistent CTA (the grid is sized to the
+// resident CTA slots of the 148 SMs, so there is no wave tail).  A range is processed as a sequence of
+// segments (one plane group, output rows [o0, o1)); a segment that starts inside a plane pays one
+// warm-up body.  Cuts closer than SNAP rows to a plane boundary snap onto it.
+FLR_DEV int cta_cut(const Params& p, int c, int align, int snap) {
+    if (c >= p.ncta) return p.rows_total;
+    const long long t = (long long)c * p.rows_total / p.ncta;
+    int pg = (int)(t / p.OH), o = (int)(t - (long long)pg * p.OH);
+    if (o < snap) o = 0;
+    else if (p.OH - o < snap) { o = 0; pg++; }
+    o -= o % align;
+    return pg * p.OH + o;
+}
+
+// geometry of one segment (uniform values)
 struct CtaGeom {
     int plane0, o0, o1, j_b0, q_b0, row0 /* global input row of stage 0, row 0 */, nbodies, nstages_total;
 };
 
 template <class C>
-FLR_DEV CtaGeom cta_geom(const Params& p, int block) {
+FLR_DEV CtaGeom seg_geom(const Params& p, int gr, int r1) {
     CtaGeom g;
-    const int pg = block / p.nbands, band = block % p.nbands;
+    const int pg = gr / p.OH;
     g.plane0 = pg * p.P;
-    g.o0 = band * p.BO;
-    g.o1 = g.o0 + p.BO < p.OH ? g.o0 + p.BO : p.OH;
+    g.o0 = gr - pg * p.OH;
+    g.o1 = g.o0 + (r1 - gr) < p.OH ? g.o0 + (r1 - gr) : p.OH;
     g.j_b0 = C::DOWN * g.o0;
     g.q_b0 = g.j_b0 / C::UP;
     g.row0 = g.q_b0 + p.cminY + (C::WLY - 1) - C::RS;
@@ -212,12 +230,13 @@ struct Stream {
     //  the generic path, exactly like an unsupported filter shape.)
     FLR_DEV void act(const Params& p, f2 v[2], uint32_t& code) {
         if (MODE == SIGN_READ) {
-            float e[4] = {v[0].x, v[0].y, v[1].x, v[1].y};
-            FLR_UNROLL for (int m = 0; m < 4; m++) if (code & (1u << (2 * m))) e[m] *= p.slope;
+            float m[4];
+            FLR_UNROLL for (int i = 0; i < 4; i++) m[i] = (code & (1u << (2 * i))) ? p.slope : 1.f;
             if (code & 0xaau) {                     // "clamped" codes written by the generic forward path
-                FLR_UNROLL for (int m = 0; m < 4; m++) if (code & (2u << (2 * m))) e[m] = 0.f;
+                FLR_UNROLL for (int i = 0; i < 4; i++) if (code & (2u << (2 * i))) m[i] = 0.f;
             }
-            v[0] = mk2(e[0], e[1]); v[1] = mk2(e[2], e[3]);
+            const f2 z = mk2(0.f, 0.f);
+            v[0] = ffma2(v[0], mk2(m[0], m[1]), z); v[1] = ffma2(v[1], mk2(m[2], m[3]), z);
         } else {
             if (MODE == SIGN_WRITE) {
                 const uint32_t u0 = f_bits(v[0].x), u1 = f_bits(v[0].y), u2 = f_bits(v[1].x), u3 = f_bits(v[1].y);
@@ -230,12 +249,9 @@ struct Stream {
         }
     }
 
-    FLR_DEV uint32_t read_code(const Params& p, int j) const {
-        const int my = j + p.sy;
-        if (my < 0 || my >= p.mask_h) return 0u;
-        const uint8_t* r = mrow0 + (int64_t)my * p.mask_pitch;
-        uint32_t b0 = (rd_byte >= 0 && rd_byte < p.mask_pitch) ? r[rd_byte] : 0u;
-        uint32_t b1 = (rd_shift && rd_byte + 1 >= 0 && rd_byte + 1 < p.mask_pitch) ? r[rd_byte + 1] : 0u;
+    // READ: sign codes of one up-res row from the staged mask rows (stage_mask); bytes outside the mask are zero there
+    FLR_DEV uint32_t read_code(const Params& p, const uint8_t* mrow) const {
+        const uint32_t b0 = mrow[rd_byte - p.mws], b1 = mrow[rd_byte - p.mws + 1];
         return (((b1 << 8) | b0) >> rd_shift) & 0xffu & colmask;
     }
 
@@ -244,7 +260,8 @@ struct Stream {
     //   grow0 : global input row index of that first row
     //   jb    : global up-res row index of the body's first row
     //   Dbuf  : this unit's KO x dp floats of the D buffer being filled
-    FLR_DEV void body(const Params& p, const T* xtile, int grow0, int jb, float* Dbuf) {
+    //   Mrows : READ: this unit's PB staged mask rows of the body
+    FLR_DEV void body(const Params& p, const T* xtile, int grow0, int jb, float* Dbuf, const uint8_t* Mrows) {
         FLR_UNROLL for (int jl = 0; jl < C::PB; jl++) {
             const int phi = jl % C::UP, qq = jl / C::UP;
             if (phi == 0) {
@@ -255,7 +272,7 @@ struct Stream {
             }
             const int j = jb + jl;
             uint32_t code = 0;
-            if (MODE == SIGN_READ) code = read_code(p, j);
+            if (MODE == SIGN_READ) code = read_code(p, Mrows + jl * p.mstride);
             // vertical polyphase up-FIR (taps carry UP * gain)
             f2 v[2] = {mk2(0.f, 0.f), mk2(0.f, 0.f)};
             FLR_UNROLL for (int k = 0; k < C::NTU; k++) {
@@ -292,6 +309,23 @@ struct Stream {
         }
     }
 };
+
+// ------------------------------------------------------------------------------------------------
+// READ mode: copy the mask rows of one body (up-res rows jb .. jb+PB-1 of every plane of the group, window
+// [mws, mws + 4*mnw) bytes) into shared memory; positions outside the mask become zero (= "pass").
+// copy4(dst, src, ok) moves one aligned 32-bit word (cp.async on the device) or zero-fills when !ok.
+// ------------------------------------------------------------------------------------------------
+template <class C, class CP>
+FLR_DEV void stage_mask(const Params& p, const CtaGeom& cg, int jb, int tid, int nthreads, uint8_t* Mdst, CP copy4) {
+    const int nwords = p.P * C::PB * p.mnw;
+    for (int w = tid; w < nwords; w += nthreads) {
+        const int t = w / p.mnw, i = w - t * p.mnw, u = t / C::PB, jl = t - u * C::PB;
+        const int my = jb + jl + p.sy, plane = cg.plane0 + u, byte = p.mws + 4 * i;
+        const bool ok = plane < p.NC && my >= 0 && my < p.mask_h && byte >= 0 && byte < p.mask_pitch;
+        const uint8_t* src = ok ? p.mask + ((int64_t)plane * p.mask_h + my) * p.mask_pitch + byte : p.mask;
+        copy4(Mdst + (size_t)t * p.mstride + 4 * i, src, ok);
+    }
+}
 
 // ------------------------------------------------------------------------------------------------
 // horizontal down-FIR of the finished rows of one body; writes y.  Called by every thread.

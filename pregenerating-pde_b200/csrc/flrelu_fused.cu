@@ -10,14 +10,6 @@ extern template int launch_cfg<__half>(const Plan&, const CUtensorMap&, int, cud
 using namespace flr;
 using namespace flr_impl;
 
-namespace {
-int env_bands() {
-    static int v = -1;
-    if (v < 0) { const char* s = getenv("CNO_FLR_BANDS"); v = s ? atoi(s) : 0; if (v < 0) v = 0; }
-    return v;
-}
-
-}  // namespace
 
 extern "C" int cno_filtered_lrelu_query(int dtype, int in_h, int in_w, int out_h, int out_w, int fu_taps,
                                         int fd_taps, int up, int down, int px0, int py0) {
@@ -45,12 +37,15 @@ extern "C" int cno_filtered_lrelu(const void* x, void* y, const void* b, uint8_t
     if (((uintptr_t)x & 15u) || ((uintptr_t)y & 15u)) return -1;
     Plan plan;
     if (make_plan(plan, cno_dtype_size(dtype), n, c, in_h, in_w, out_h, out_w, fu, fu_taps, fd, fd_taps, up, down,
-                  px0, py0, gain, slope, clamp, flip, env_bands()) != 0) return -1;
+                  px0, py0, gain, slope, clamp, flip, env_ctas()) != 0) return -1;
     Params& p = plan.p;
     if (sign_mode == CNO_SIGN_WRITE)
         CNO_CHECK_ARG(mask_h >= p.UH && mask_pitch >= p.G, "filtered_lrelu: mask [%d rows x %d bytes] smaller than [%d x %d]", mask_h, mask_pitch, p.UH, p.G);
     p.y = y; p.b = b; p.mask = mask; p.db = nullptr;
-    { const char* d = getenv("CNO_FLR_DEBUG"); p.dbg = d ? atoi(d) : 0; }
+    if (sign_mode == CNO_SIGN_READ) {
+        if (((uintptr_t)mask & 3u) || (mask_pitch & 3)) return -1;     // staged with aligned 32-bit copies
+        set_mask_window(plan, sx);
+    }
     p.mask_h = mask_h; p.mask_w = mask_w; p.mask_pitch = mask_pitch; p.sx = sx; p.sy = sy;
 
     EncodeTiledFn enc = get_encode();

@@ -61,8 +61,12 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     uint8_t* xst = smem;
     float* D = reinterpret_cast<float*>(smem + (size_t)NSTAGE * p.stage_bytes);
     uint64_t* bars = reinterpret_cast<uint64_t*>(D + (size_t)2 * p.P * C::KO * p.dp);
+    uint8_t* M = reinterpret_cast<uint8_t*>(bars) + 64;                 // READ: 2 x [P][PB][mstride] staged mask rows
+    const size_t mbuf = (size_t)p.P * C::PB * p.mstride;
+    auto copy4 = [](uint8_t* dst, const uint8_t* src, bool ok) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(ok ? 4 : 0) : "memory");
+    };
     const int tid = threadIdx.x;
-    const CtaGeom cg = cta_geom<C>(p, blockIdx.x);
     const uint32_t stage_tx = (uint32_t)(p.P * C::RS * p.bwx * (int)sizeof(T));
 
     if (tid == 0) {
@@ -70,25 +74,6 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
-    __syncthreads();
-    if (p.dbg == 1) return;
-    int next_load = 0;
-    auto issue = [&](int s) {
-        const int slot = s % NSTAGE;
-        mbar_expect_tx(&bars[slot], stage_tx);
-        tma_load_3d(xst + (size_t)slot * p.stage_bytes, &tmap, &bars[slot], p.tmaX, cg.row0 + s * C::RS, cg.plane0);
-    };
-    if (tid == 0) while (next_load < cg.nstages_total && next_load < NSTAGE) issue(next_load++);
-
-    Stream<T, C, MODE> st;
-    st.init(p, cg, tid, [&](int ch) { return Cvt<T>::get(reinterpret_cast<const T*>(p.b)[ch]); });
-
-    if (p.dbg == 2) return;
-    mbar_wait(&bars[0], 0);
-    if (p.dbg == 3) return;
-    if (st.active) st.prologue(p, reinterpret_cast<const T*>(xst) + (size_t)st.unit * C::RS * p.bwx, cg.row0);
-
-    if (p.dbg == 4) { if (st.active && st.win[0][0].x == 12345.f) reinterpret_cast<float*>(p.y)[0] = 1.f; return; }
     const bool vec_ok = (p.OW & 3) == 0;
     T* const yb = reinterpret_cast<T*>(p.y);
     auto store4 = [&](int plane, int o, int ox, const float* out) {
@@ -100,20 +85,48 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         }
     };
 
-    for (int k = 0; k < cg.nbodies; k++) {
-        const int s = 1 + k / C::M, slot = s % NSTAGE, sub = k % C::M;
-        if (sub == 0) mbar_wait(&bars[slot], (uint32_t)((s / NSTAGE) & 1));
-        if (st.active)
-            st.body(p, reinterpret_cast<const T*>(xst + (size_t)slot * p.stage_bytes) + ((size_t)st.unit * C::RS + sub * C::PQ) * p.bwx,
-                    cg.row0 + s * C::RS + sub * C::PQ, cg.j_b0 + k * C::PB,
-                    D + ((size_t)(k & 1) * p.P + st.unit) * C::KO * p.dp);
-        __syncthreads();
-        if (p.dbg == 5) return;
-        if (tid == 0) {
-            const int consumed = 1 + (k + 1) / C::M;
-            while (next_load < cg.nstages_total && next_load < consumed + NSTAGE) issue(next_load++);
+    // this CTA's range of the global row space, processed segment by segment
+    const int r0 = cta_cut(p, blockIdx.x, C::ALIGN, C::SNAP), r1 = cta_cut(p, blockIdx.x + 1, C::ALIGN, C::SNAP);
+    int gs0 = 0;                                  // x stages issued by earlier segments (slot / parity bookkeeping)
+    for (int gr = r0; gr < r1;) {
+        const CtaGeom cg = seg_geom<C>(p, gr, r1);
+        __syncthreads();                          // barrier init visible; previous segment's D buffers and x stages are free
+        int next_load = 0;
+        auto issue = [&](int s) {
+            const int slot = (gs0 + s) % NSTAGE;
+            mbar_expect_tx(&bars[slot], stage_tx);
+            tma_load_3d(xst + (size_t)slot * p.stage_bytes, &tmap, &bars[slot], p.tmaX, cg.row0 + s * C::RS, cg.plane0);
+        };
+        if (tid == 0) while (next_load < cg.nstages_total && next_load < NSTAGE) issue(next_load++);
+
+        Stream<T, C, MODE> st;
+        st.init(p, cg, tid, [&](int ch) { return Cvt<T>::get(reinterpret_cast<const T*>(p.b)[ch]); });
+
+        if (MODE == SIGN_READ) stage_mask<C>(p, cg, cg.j_b0, tid, blockDim.x, M, copy4);
+        mbar_wait(&bars[gs0 % NSTAGE], (uint32_t)((gs0 / NSTAGE) & 1));
+        if (st.active) st.prologue(p, reinterpret_cast<const T*>(xst + (size_t)(gs0 % NSTAGE) * p.stage_bytes) + (size_t)st.unit * C::RS * p.bwx, cg.row0);
+        if (MODE == SIGN_READ) { asm volatile("cp.async.wait_all;" ::: "memory"); __syncthreads(); }
+
+        for (int k = 0; k < cg.nbodies; k++) {
+            const int s = 1 + k / C::M, slot = (gs0 + s) % NSTAGE, sub = k % C::M;
+            if (MODE == SIGN_READ && k + 1 < cg.nbodies)                 // next body's mask rows, in flight during this body
+                stage_mask<C>(p, cg, cg.j_b0 + (k + 1) * C::PB, tid, blockDim.x, M + (size_t)((k + 1) & 1) * mbuf, copy4);
+            if (sub == 0) mbar_wait(&bars[slot], (uint32_t)(((gs0 + s) / NSTAGE) & 1));
+            if (st.active)
+                st.body(p, reinterpret_cast<const T*>(xst + (size_t)slot * p.stage_bytes) + ((size_t)st.unit * C::RS + sub * C::PQ) * p.bwx,
+                        cg.row0 + s * C::RS + sub * C::PQ, cg.j_b0 + k * C::PB,
+                        D + ((size_t)(k & 1) * p.P + st.unit) * C::KO * p.dp,
+                        M + (size_t)(k & 1) * mbuf + (size_t)st.unit * C::PB * p.mstride);
+            if (MODE == SIGN_READ) asm volatile("cp.async.wait_all;" ::: "memory");
+            __syncthreads();
+            if (tid == 0) {
+                const int consumed = 1 + (k + 1) / C::M;
+                while (next_load < cg.nstages_total && next_load < consumed + NSTAGE) issue(next_load++);
+            }
+            hdown_phase<T, C>(p, cg, tid, blockDim.x, k, D + (size_t)(k & 1) * p.P * C::KO * p.dp, store4);
         }
-        hdown_phase<T, C>(p, cg, tid, blockDim.x, k, D + (size_t)(k & 1) * p.P * C::KO * p.dp, store4);
+        gs0 += cg.nstages_total;
+        gr += cg.o1 - cg.o0;
     }
 }
 
@@ -131,6 +144,12 @@ inline EncodeTiledFn get_encode() {
     return fn;
 }
 
+inline int env_ctas() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("CNO_FLR_CTAS"); v = e ? atoi(e) : 0; if (v < 0) v = 0; }
+    return v;
+}
+
 template <class T, class C, int MODE>
 int launch_variant(const Plan& plan, const CUtensorMap& map, cudaStream_t st) {
     auto kern = flr_fused_kernel<T, C, MODE>;
@@ -140,7 +159,18 @@ int launch_variant(const Plan& plan, const CUtensorMap& map, cudaStream_t st) {
         if (e != cudaSuccess) { cno_set_error("filtered_lrelu: cannot reserve %zu bytes of shared memory: %s", plan.smem_bytes, cudaGetErrorString(e)); return (int)e; }
         configured = plan.smem_bytes;
     }
-    kern<<<plan.blocks, plan.threads, plan.smem_bytes, st>>>(map, plan.p);
+    // persistent grid: one CTA per resident slot (occupancy x SM count), cached per (threads, smem)
+    static int occ_threads = 0, occ_ctas = 0; static size_t occ_smem = 0;
+    if (occ_threads != plan.threads || occ_smem != plan.smem_bytes) {
+        int per_sm = 0, dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, plan.threads, plan.smem_bytes) != cudaSuccess || per_sm < 1) per_sm = 1;
+        occ_ctas = per_sm * sms; occ_threads = plan.threads; occ_smem = plan.smem_bytes;
+    }
+    Plan pl = plan;
+    if (env_ctas() == 0) set_partition(pl, occ_ctas);
+    kern<<<pl.blocks, pl.threads, pl.smem_bytes, st>>>(map, pl.p);
     CNO_LAUNCH_CHECK();
     return 0;
 }

@@ -36,11 +36,27 @@ static inline bool variant_compiled(int up, int down, int rx, int ry) {
     return false;
 }
 
+// number of persistent CTAs: every resident slot, but at least two bodies of output rows per CTA
+static inline void set_partition(Plan& plan, int max_ctas, bool forced = false) {
+    Params& p = plan.p;
+    int n = forced ? max_ctas : p.rows_total / 12;
+    if (n > max_ctas) n = max_ctas;
+    if (n > p.rows_total) n = p.rows_total;
+    if (n < 1) n = 1;
+    p.ncta = n; plan.blocks = n;
+}
+
+// READ mode: window of mask bytes a row of threads touches, for the sign offset sx (call after make_plan)
+static inline void set_mask_window(Plan& plan, int sx) {
+    const int wb0 = floor_div_i(sx, 4);                // byte of column group 0
+    plan.p.mws = floor_div_i(wb0, 4) * 4;
+}
+
 // returns 0 and fills `plan`, or -1 when the fused kernel does not cover the arguments
 static inline int make_plan(Plan& plan, int elem_size, int n, int c, int in_h, int in_w, int out_h, int out_w,
                             const float* fu, int fu_taps, const float* fd, int fd_taps, int up, int down,
                             int px0, int py0, float gain, float slope, float clamp, int flip,
-                            int forced_bands /* 0 = heuristic */) {
+                            int forced_ctas /* 0 = heuristic */) {
     memset(&plan, 0, sizeof(plan));
     if (!((up == 2 || up == 4) && (down == 2 || down == 4))) return -1;
     if (fu_taps != 6 * up || fd_taps != 6 * down) return -1;
@@ -73,30 +89,22 @@ static inline int make_plan(Plan& plan, int elem_size, int n, int c, int in_h, i
     p.ncq_shift = -1;
     for (int s = 0; s < 16; s++) if ((1 << s) == p.ncq) p.ncq_shift = s;
     const int rs = variant_rs(up, down, ry);
+    const int mstride = ((p.G + 4 + 3) / 4) * 4;                      // staged mask row (READ mode): G + 1 bytes at any 4-byte phase
+    p.mstride = mstride; p.mnw = mstride / 4; p.mws = 0;
     // planes per CTA: fill up to 256 threads, stay inside ~100 KB of shared memory (2 CTAs / SM)
     int P = 256 / p.G; if (P < 1) P = 1; if (P > p.NC) P = p.NC;
     for (;; P--) {
         const size_t stage = ((size_t)P * rs * bwx * elem_size + 127) / 128 * 128;
-        const size_t total = NSTAGE * stage + (size_t)2 * P * 6 * p.dp * 4 + 64;
+        const size_t total = NSTAGE * stage + (size_t)2 * P * 6 * p.dp * 4 + 64 + (size_t)2 * P * (6 * down) * mstride;
         if (total <= 100 * 1024 || P == 1) { p.stage_bytes = (int)stage; plan.smem_bytes = total; break; }
     }
     if (plan.smem_bytes > 220 * 1024) return -1;
     p.P = P;
     plan.threads = (P * p.G + 31) / 32 * 32;
     if (plan.threads > 256) { /* G > 256/P cannot happen */ return -1; }
-    // bands: split tall planes when there are too few plane groups to fill 2 x 148 CTAs
-    const int groups = (p.NC + P - 1) / P;
-    int nb = 1;
-    if (forced_bands > 0) nb = forced_bands;
-    else {
-        while (groups * nb < 2 * 148 && out_h / (nb * 2) >= 24) nb *= 2;
-    }
-    int bo = (out_h + nb - 1) / nb;
-    const int align = (up == 4 && down == 2) ? 2 : 1;                  // band start must be a whole input row
-    bo = (bo + align - 1) / align * align;
-    nb = (out_h + bo - 1) / bo;
-    p.nbands = nb; p.BO = bo;
-    plan.blocks = groups * nb;
+    // persistent CTAs over the global row space (flrelu_core.h cta_cut); finalised by set_partition()
+    p.rows_total = ((p.NC + P - 1) / P) * out_h;
+    set_partition(plan, forced_ctas > 0 ? forced_ctas : 2 * 148, forced_ctas > 0);
     if (clamp >= 0.f && clamp < 3.0e38f) return -1;                   // clamp: generic composition
     if (!(slope >= 0.f && slope <= 1.f)) return -1;                   // lrelu as max(v, slope*v)
     p.slope = slope;

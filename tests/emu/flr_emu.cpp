@@ -23,29 +23,42 @@ static void run(const Plan& plan, const float* x, float* y, const float* bias) {
             dst[((size_t)u * C::RS + r) * p.bwx + cidx] = v;
         }
     };
+    const size_t mbuf = (size_t)p.P * C::PB * p.mstride;
+    std::vector<uint8_t> M(2 * mbuf, 0xAA);                     // 0xAA = "clamped" everywhere: catches reads of unstaged bytes
+    auto copy4 = [](uint8_t* dst, const uint8_t* src, bool ok) { if (ok) memcpy(dst, src, 4); else memset(dst, 0, 4); };
     auto store4 = [&](int plane, int o, int ox, const float* out) {
         for (int i = 0; i < 4; i++) if (ox + i < p.OW) y[((size_t)plane * p.OH + o) * p.OW + ox + i] = out[i];
     };
     for (int blk = 0; blk < plan.blocks; blk++) {
-        const CtaGeom cg = cta_geom<C>(p, blk);
-        std::vector<Stream<float, C, MODE>> th(nthreads);
-        int next_load = 0;
-        auto issue = [&](int s) { tma(s % NSTAGE, cg.row0 + s * C::RS, cg.plane0); };
-        while (next_load < cg.nstages_total && next_load < NSTAGE) issue(next_load++);
-        for (int t = 0; t < nthreads; t++) {
-            th[t].init(p, cg, t, [&](int ch) { return bias[ch]; });
-            if (th[t].active) th[t].prologue(p, xst.data() + (size_t)th[t].unit * C::RS * p.bwx, cg.row0);
-        }
-        for (int k = 0; k < cg.nbodies; k++) {
-            const int s = 1 + k / C::M, slot = s % NSTAGE;
-            for (int t = 0; t < nthreads; t++) if (th[t].active)
-                th[t].body(p, xst.data() + (size_t)slot * p.P * C::RS * p.bwx + ((size_t)th[t].unit * C::RS + (k % C::M) * C::PQ) * p.bwx,
-                           cg.row0 + s * C::RS + (k % C::M) * C::PQ, cg.j_b0 + k * C::PB,
-                           D.data() + ((size_t)(k & 1) * p.P + th[t].unit) * C::KO * p.dp);
-            const int consumed = 1 + (k + 1) / C::M;
-            while (next_load < cg.nstages_total && next_load < consumed + NSTAGE) issue(next_load++);
-            for (int t = 0; t < nthreads; t++)
-                hdown_phase<float, C>(p, cg, t, nthreads, k, D.data() + (size_t)(k & 1) * p.P * C::KO * p.dp, store4);
+        const int r0 = cta_cut(p, blk, C::ALIGN, C::SNAP), r1 = cta_cut(p, blk + 1, C::ALIGN, C::SNAP);
+        int gs0 = 0;
+        for (int gr = r0; gr < r1;) {
+            const CtaGeom cg = seg_geom<C>(p, gr, r1);
+            std::vector<Stream<float, C, MODE>> th(nthreads);
+            int next_load = 0;
+            auto issue = [&](int s) { tma((gs0 + s) % NSTAGE, cg.row0 + s * C::RS, cg.plane0); };
+            while (next_load < cg.nstages_total && next_load < NSTAGE) issue(next_load++);
+            if (MODE == SIGN_READ) for (int t = 0; t < nthreads; t++) stage_mask<C>(p, cg, cg.j_b0, t, nthreads, M.data(), copy4);
+            for (int t = 0; t < nthreads; t++) {
+                th[t].init(p, cg, t, [&](int ch) { return bias[ch]; });
+                if (th[t].active) th[t].prologue(p, xst.data() + ((size_t)(gs0 % NSTAGE) * p.P + th[t].unit) * C::RS * p.bwx, cg.row0);
+            }
+            for (int k = 0; k < cg.nbodies; k++) {
+                const int s = 1 + k / C::M, slot = (gs0 + s) % NSTAGE;
+                if (MODE == SIGN_READ && k + 1 < cg.nbodies) for (int t = 0; t < nthreads; t++)
+                    stage_mask<C>(p, cg, cg.j_b0 + (k + 1) * C::PB, t, nthreads, M.data() + (size_t)((k + 1) & 1) * mbuf, copy4);
+                for (int t = 0; t < nthreads; t++) if (th[t].active)
+                    th[t].body(p, xst.data() + (size_t)slot * p.P * C::RS * p.bwx + ((size_t)th[t].unit * C::RS + (k % C::M) * C::PQ) * p.bwx,
+                               cg.row0 + s * C::RS + (k % C::M) * C::PQ, cg.j_b0 + k * C::PB,
+                               D.data() + ((size_t)(k & 1) * p.P + th[t].unit) * C::KO * p.dp,
+                               M.data() + (size_t)(k & 1) * mbuf + (size_t)th[t].unit * C::PB * p.mstride);
+                const int consumed = 1 + (k + 1) / C::M;
+                while (next_load < cg.nstages_total && next_load < consumed + NSTAGE) issue(next_load++);
+                for (int t = 0; t < nthreads; t++)
+                    hdown_phase<float, C>(p, cg, t, nthreads, k, D.data() + (size_t)(k & 1) * p.P * C::KO * p.dp, store4);
+            }
+            gs0 += cg.nstages_total;
+            gr += cg.o1 - cg.o0;
         }
     }
 }
@@ -60,13 +73,14 @@ static void run_mode(const Plan& plan, int mode, const float* x, float* y, const
 extern "C" int flr_emulate(const float* x, float* y, const float* b, uint8_t* mask, int n, int c, int in_h, int in_w,
                            int out_h, int out_w, const float* fu, int fu_taps, const float* fd, int fd_taps, int up,
                            int down, int px0, int py0, int mask_h, int mask_w, int mask_pitch, int sx, int sy,
-                           int mode, float gain, float slope, float clamp, int flip, int bands, int* info) {
+                           int mode, float gain, float slope, float clamp, int flip, int ctas, int* info) {
     Plan plan;
     if (make_plan(plan, 4, n, c, in_h, in_w, out_h, out_w, fu, fu_taps, fd, fd_taps, up, down, px0, py0, gain, slope,
-                  clamp, flip, bands) != 0) return -1;
+                  clamp, flip, ctas) != 0) return -1;
     plan.p.b = b; plan.p.mask = mask; plan.p.mask_h = mask_h; plan.p.mask_w = mask_w; plan.p.mask_pitch = mask_pitch;
     plan.p.sx = sx; plan.p.sy = sy;
-    if (info) { info[0] = plan.p.P; info[1] = plan.threads; info[2] = plan.blocks; info[3] = plan.p.nbands; info[4] = (int)plan.smem_bytes; }
+    if (mode == SIGN_READ) set_mask_window(plan, sx);
+    if (info) { info[0] = plan.p.P; info[1] = plan.threads; info[2] = plan.blocks; info[3] = plan.p.ncta; info[4] = (int)plan.smem_bytes; }
 #define V(U, D, R) if (plan.up == U && plan.down == D && plan.rx == R && plan.ry == R) { run_mode<Cfg<U, D, R, R>>(plan, mode, x, y, b); return 0; }
     V(2, 2, 0) V(2, 2, 1) V(2, 4, 0) V(2, 4, 1) V(4, 2, 0) V(4, 2, 1) V(4, 2, 2) V(4, 2, 3)
 #undef V

@@ -50,11 +50,11 @@ def rel(a, b):
     return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
 
 
-CASES = [  # name, in, out, N, C, bands
+CASES = [  # name, in, out, N, C, forced number of persistent CTAs (0 = heuristic)
     ('I', 16, 16, 2, 3, 0), ('D', 16, 8, 2, 3, 0), ('U', 8, 16, 2, 3, 0),
     ('I', 32, 32, 1, 5, 0), ('D', 32, 16, 1, 2, 0), ('U', 16, 32, 1, 2, 0),
-    ('I', 64, 64, 1, 2, 2), ('D', 64, 32, 1, 2, 2), ('U', 32, 64, 1, 3, 2), ('I', 128, 128, 1, 1, 4),
-    ('I', 8, 8, 3, 40, 0),
+    ('I', 64, 64, 1, 2, 2), ('D', 64, 32, 1, 2, 3), ('U', 32, 64, 1, 3, 5), ('I', 128, 128, 1, 1, 4),
+    ('I', 8, 8, 3, 40, 0), ('I', 32, 32, 2, 9, 7), ('U', 16, 32, 2, 9, 11), ('D', 32, 16, 3, 7, 6),
 ]
 
 
