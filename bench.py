@@ -123,7 +123,6 @@ def run_reference_arm(args):
 def run_ours(args):
     import torch.distributed as dist
     import pregenerating_pde_b200 as cno
-    from oracle import cno_oracle as O       # filter design + the cpu_baseline checker leg only
     world = int(os.environ.get('WORLD_SIZE', '1'))
     rank = int(os.environ.get('RANK', '0'))
     local = int(os.environ.get('LOCAL_RANK', '0'))
@@ -133,8 +132,9 @@ def run_ours(args):
         dist.init_process_group('nccl', device_id=dev)
     cno._lib.load()
     W = WORKLOAD
-    cfg = O.lrelu_config(W['S_in'], W['S_out'])
-    fu, fd = cfg['fu'].to(dev), cfg['fd'].to(dev)
+    act = cno.cno_model.lrelu_for(W['C'], W['S_in'], W['S_out']).to(dev)      # filters / padding exactly as CNOBlock builds them
+    cfg = dict(up=act.up_factor, down=act.down_factor, padding=act.padding, fd=act.down_filter)
+    fu, fd = act.up_filter, act.down_filter
     g = torch.Generator(device=dev).manual_seed(rank)
     x = torch.randn(W['N'], W['C'], W['S_in'], W['S_in'], device=dev, generator=g)
     b = torch.randn(W['C'], device=dev, generator=g)
@@ -236,8 +236,69 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_cno_train(args):
+    """Secondary workload (BASELINE.json configs[2], [3]): CNO_time (TrainCNO_time_L configuration, 18.28 M parameters) training
+    step on synthetic FPO batches, batch 32 per GPU, DDP over NCCL for N > 1; value = samples/s over all GPUs."""
+    import torch.distributed as dist
+    import pregenerating_pde_b200 as cno
+    world = int(os.environ.get('WORLD_SIZE', '1')); rank = int(os.environ.get('RANK', '0')); local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    torch.backends.cudnn.benchmark = True
+    B = args.batch
+    tr = cno.train.Trainer(device=dev, ddp=world > 1, graph=args.graph and world == 1)
+    batches = [cno.train.synthetic_fpo_batch(B, device='cpu', seed=100 * rank + i) for i in range(2)]
+    host = [tuple(v.pin_memory() for v in b) for b in batches]
+    devb = [tuple(v.to(dev) for v in b) for b in batches]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    for i in range(max(args.warmup, 3)):
+        tr.step(*devb[i % 2])
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier(); e0.record()
+    for i in range(args.steps):
+        loss = tr.step(*devb[i % 2])
+    e1.record(); barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    # end to end: batch from pinned host memory every step, loss read back every step
+    barrier(); t0 = time.perf_counter()
+    for i in range(args.steps):
+        b = tuple(v.to(dev, non_blocking=True) for v in host[i % 2])
+        lv = float(tr.step(*b))
+    barrier(); e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    tt = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = tt.tolist()
+    if rank == 0:
+        h2d = sum(v.numel() * v.element_size() for v in host[0])
+        print(json.dumps({
+            'metric': 'cno_train_samples_per_s', 'value': round(world * B / (ms * 1e-3), 2), 'unit': 'samples/s', 'n_gpus': world,
+            'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': round(ms, 3), 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': 'CNO_time TrainCNO_time_L config (N_layers 4, N_res 8, 18.28M params) fwd + rel-L1 + bwd + AdamW, FPO 7ch 128x128',
+                       'batch_per_gpu': B, 'cuda_graph': bool(tr.use_graph), 'parallelism': f'dp{world}', 'final_loss': round(float(loss), 5)},
+            'e2e': {'value': round(world * B / (e2e_ms * 1e-3), 2), 'unit': 'samples/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 4,
+                    'ms_per_step': round(e2e_ms, 3)},
+            'clocks': clocks}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument('--workload', default='flr', choices=['flr', 'cno_train'])
+    ap.add_argument('--batch', type=int, default=32)
+    ap.add_argument('--graph', type=int, default=1)
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=30)
     ap.add_argument('--warmup', type=int, default=5)
@@ -249,6 +310,8 @@ def main():
         return bench_sweep.main()
     if args.impl == 'reference':
         return run_reference_arm(args)
+    if args.workload == 'cno_train':
+        return run_cno_train(args)
     return run_ours(args)
 
 

@@ -1,0 +1,76 @@
+"""The CNO_time mirror (callers of the hot path) against golden vectors produced by the unmodified reference
+model (oracle/make_golden_model.py): identical state_dict keys, forward, loss and gradients.
+CPU: the mirror runs impl='ref'-equivalent torch ops (no CUDA tensor -> the package's ref definitions);
+GPU: the same checkpoint through the sm_100a kernels."""
+import os, sys
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+CFG = dict(in_dim=5, in_size=32, N_layers=2, N_res=1, N_res_neck=2, channel_multiplier=8, out_dim=3, is_time=1,
+           nl_dim=[2, 3], latent_lift_proj_dim=16)
+
+
+def _load(golden):
+    g = golden['cno_model']
+    sd = {k[3:]: torch.from_numpy(g[k]) for k in g.files if k.startswith('sd.')}
+    return g, sd
+
+
+def _build(dev):
+    import pregenerating_pde_b200 as pkg
+    from pregenerating_pde_b200 import cno_model
+    return cno_model.CNO_time(**CFG).to(dev)
+
+
+def _rel(a, b):
+    a, b = torch.as_tensor(a).detach().double().cpu(), torch.as_tensor(b).detach().double().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def _check(golden, dev, tol):
+    g, sd = _load(golden)
+    model = _build(dev)
+    assert sorted(model.state_dict().keys()) == sorted(sd.keys())            # checkpoint compatibility
+    model.load_state_dict(sd, strict=True)
+    assert sum(p.numel() for p in model.parameters()) == int(g['n_params'])
+    x, t, target = (torch.from_numpy(g[k]).to(dev) for k in ('x', 't', 'target'))
+    y = model(x, t)
+    assert _rel(y, g['y']) < tol
+    loss = model.training_loss(y, target)
+    assert abs(float(loss.detach()) - float(g['loss'])) / float(g['loss']) < tol
+    loss.backward()
+    named = dict(model.named_parameters())
+    for k in g.files:
+        if k.startswith('grad.'):
+            assert _rel(named[k[5:]].grad, g[k]) < 10 * tol, k
+    # the reference builds decoder_inv[N_layers] but never calls it: same parameters stay without gradient
+    assert sorted(k for k, p in named.items() if p.grad is None) == list(g['no_grad_params'])
+
+
+def test_mirror_matches_reference_cpu(golden):
+    _check(golden, 'cpu', 2e-5)
+
+
+@pytest.mark.gpu
+def test_mirror_matches_reference_gpu(golden):
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    _check(golden, 'cuda', 5e-5)
+
+
+@pytest.mark.skipif(not os.path.isdir('/root/reference/CNO_Experiments'), reason='reference checkout not present')
+def test_mirror_key_set_full_config():
+    """full TrainCNO_time_L configuration: same parameter names / shapes as the reference (18,280,147 parameters)."""
+    import make_golden as mg
+    mg._stub_modules()
+    sys.path.insert(0, '/root/reference/CNO_Experiments')
+    import CNO_timeModule_CIN as ref
+    from pregenerating_pde_b200 import cno_model
+    cfg = cno_model.train_config_L()
+    a = ref.CNO_time(loader_dictionary={}, **cfg).state_dict()
+    b = cno_model.CNO_time(**cfg).state_dict()
+    assert {k: tuple(v.shape) for k, v in a.items()} == {k: tuple(v.shape) for k, v in b.items()}
+    assert sum(v.numel() for k, v in cno_model.CNO_time(**cfg).named_parameters()) == 18280147
