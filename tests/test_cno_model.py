@@ -45,7 +45,7 @@ def _check(golden, dev, tol):
     named = dict(model.named_parameters())
     for k in g.files:
         if k.startswith('grad.'):
-            assert _rel(named[k[5:]].grad, g[k]) < 10 * tol, k
+            assert _rel(named[k[5:]].grad, g[k]) < 10 * tol, (k, _rel(named[k[5:]].grad, g[k]))
     # the reference builds decoder_inv[N_layers] but never calls it: same parameters stay without gradient
     assert sorted(k for k, p in named.items() if p.grad is None) == list(g['no_grad_params'])
 
