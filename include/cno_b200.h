@@ -87,6 +87,23 @@ int cno_cin_bwd(const void* x, const void* dy, void* dx, const float* gamma, con
                 const float* mean, const float* rstd, float* s1, float* s2, int dtype, int n, int c,
                 int hw, void* stream);
 
+/* FILM.forward in one launch (CNO_timeModule_CIN.py:60-70 incl. the four Linear layers :64-65):
+ *   scale[n,c] = b2s[c] + sum_j W2s[c,j]*(w1s[j]*t[n] + b1s[j]),  shift likewise from the *b weights (lat = 128),
+ *   then the instance norm + affine + FiLM of cno_cin_fwd.  scale_out fp32[N,C] (optional) is kept for backward. */
+int cno_film_fwd(const void* x, void* y, const float* t, const float* gamma, const float* beta,
+                 const float* w1s, const float* b1s, const float* W2s, const float* b2s,
+                 const float* w1b, const float* b1b, const float* W2b, const float* b2b,
+                 float* scale_out, float* mean, float* rstd, int dtype, int n, int c, int hw, int lat,
+                 float eps, void* stream);
+/* every parameter gradient of one FILM module from the per-plane sums s1, s2 of cno_cin_bwd, in one launch
+ * (replaces autograd through 4 Linear layers, ~20 small kernels): dgamma, dbeta [C]; d lat2scale.weight [C,lat] / bias [C];
+ * d inp2lat_sacale.weight / bias [lat]; the same four for the shift branch.  Deterministic (no atomics). */
+int cno_film_bwd_finish(const float* s1, const float* s2, const float* t, const float* gamma, const float* beta,
+                        const float* scale, const float* w1s, const float* b1s, const float* W2s,
+                        const float* w1b, const float* b1b, const float* W2b,
+                        float* dgamma, float* dbeta, float* dW2s, float* db2s, float* dw1s, float* db1s,
+                        float* dW2b, float* db2b, float* dw1b, float* db1b, int n, int c, int lat, void* stream);
+
 /* Measurement helper used by bench.py / tests (not part of the reference surface): FP32 FMA issue
  * rate probe.  variant 0 = scalar FFMA, 1 = packed fma.rn.f32x2.  Writes elapsed-cycle-independent
  * results to out[threads]; returns 0. */

@@ -11,6 +11,9 @@ from . import _lib
 from .torch_utils.custom_ops import _DT, _ptr, _stream
 
 
+FUSE_LINEARS = True       # False: keep the four Linear layers in torch (autograd supports higher-order gradients there)
+
+
 class _Cin(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, scale, shift, eps):
@@ -64,15 +67,80 @@ def cin(x, gamma, beta, scale, shift, eps=1e-5):
     return _Cin.apply(x, gamma, beta, scale, shift, eps)
 
 
+class _Film(torch.autograd.Function):
+    """FILM.forward as one kernel (scale / shift from the four Linear layers computed in the kernel prologue) and a
+    backward of two kernels (cno_cin_bwd + cno_film_bwd_finish) instead of ~30 small torch launches."""
+
+    @staticmethod
+    def forward(ctx, x, t, gamma, beta, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b, eps):
+        lib = _lib.load()
+        n, c, h, w = x.shape
+        x = x.contiguous()
+        f32 = lambda v: v.detach().float().contiguous()
+        t32 = f32(t).reshape(-1)
+        P = [f32(v) for v in (gamma, beta, w1s.reshape(-1), b1s, W2s, b2s, w1b.reshape(-1), b1b, W2b, b2b)]
+        lat = P[2].numel()
+        assert t32.numel() == n and P[4].shape == (c, lat) and P[8].shape == (c, lat)
+        y = torch.empty_like(x)
+        mean = torch.empty([n, c], dtype=torch.float32, device=x.device)
+        rstd, scale = torch.empty_like(mean), torch.empty_like(mean)
+        with torch.cuda.device(x.device):
+            rc = lib.cno_film_fwd(_ptr(x), _ptr(y), _ptr(t32), *[_ptr(v) for v in P], _ptr(scale), _ptr(mean), _ptr(rstd),
+                                  _DT[x.dtype], n, c, h * w, lat, float(eps), _stream(x))
+        _lib.check(rc, 'film_fwd')
+        ctx.save_for_backward(x, t32, scale, mean, rstd, *P)
+        ctx.meta = [(v.dtype, v.shape) for v in (gamma, beta, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b)]
+        return y
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, dy):
+        lib = _lib.load()
+        x, t32, scale, mean, rstd, gamma, beta, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b = ctx.saved_tensors
+        n, c, h, w = x.shape
+        lat = w1s.numel()
+        dy = dy.contiguous()
+        dx = torch.empty_like(x)
+        s12 = torch.empty([2, n, c], dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            rc = lib.cno_cin_bwd(_ptr(x), _ptr(dy), _ptr(dx), _ptr(gamma), _ptr(scale), _ptr(mean), _ptr(rstd), _ptr(s12[0]), _ptr(s12[1]),
+                                 _DT[x.dtype], n, c, h * w, _stream(x))
+            _lib.check(rc, 'cin_bwd')
+            # one flat buffer for the ten parameter gradients
+            sizes = [c, c, lat, lat, c * lat, c, lat, lat, c * lat, c]      # dgamma dbeta dw1s db1s dW2s db2s dw1b db1b dW2b db2b
+            flat = torch.empty([sum(sizes)], dtype=torch.float32, device=x.device)
+            g = list(flat.split(sizes))
+            rc = lib.cno_film_bwd_finish(_ptr(s12[0]), _ptr(s12[1]), _ptr(t32), _ptr(gamma), _ptr(beta), _ptr(scale),
+                                         _ptr(w1s), _ptr(b1s), _ptr(W2s), _ptr(w1b), _ptr(b1b), _ptr(W2b),
+                                         _ptr(g[0]), _ptr(g[1]), _ptr(g[4]), _ptr(g[5]), _ptr(g[2]), _ptr(g[3]),
+                                         _ptr(g[8]), _ptr(g[9]), _ptr(g[6]), _ptr(g[7]), n, c, lat, _stream(x))
+            _lib.check(rc, 'film_bwd_finish')
+        outs = [gi.view(shape).to(dt) for gi, (dt, shape) in zip(g, ctx.meta)]
+        outs = [o if need else None for o, need in zip(outs, ctx.needs_input_grad[2:12])]
+        return (dx if ctx.needs_input_grad[0] else None, None, *outs, None)
+
+
+def _film_fusable(self, x):
+    lin = (self.inp2lat_sacale, self.lat2scale, self.inp2lat_bias, self.lat2bias)
+    return (all(isinstance(m, torch.nn.Linear) and m.bias is not None for m in lin)
+            and self.inp2lat_sacale.in_features == 1 and self.inp2lat_bias.in_features == 1
+            and self.inp2lat_sacale.out_features == self.inp2lat_bias.out_features
+            and all(m.weight.dtype == torch.float32 for m in lin) and not torch.is_autocast_enabled())
+
+
 def film_forward(self, x, timestep):
     """Replacement for FILM.forward (CNO_timeModule_CIN.py:60-70).  Uses the fused kernel when the module
     is the instance-norm flavour on a CUDA tensor; every other case runs the module's own torch ops."""
     norm = self.norm
-    t = timestep.reshape(-1, 1).type_as(x)
-    scale = self.lat2scale(self.inp2lat_sacale(t))
-    shift = self.lat2bias(self.inp2lat_bias(t))
     fused = (x.is_cuda and x.ndim == 4 and isinstance(norm, torch.nn.InstanceNorm2d) and norm.affine
              and not norm.track_running_stats and x.dtype in _DT and x.dtype != torch.float64)
+    if fused and FUSE_LINEARS and _film_fusable(self, x) and not timestep.requires_grad:
+        return _Film.apply(x, timestep, norm.weight, norm.bias, self.inp2lat_sacale.weight, self.inp2lat_sacale.bias,
+                           self.lat2scale.weight, self.lat2scale.bias, self.inp2lat_bias.weight, self.inp2lat_bias.bias,
+                           self.lat2bias.weight, self.lat2bias.bias, norm.eps)
+    t = timestep.reshape(-1, 1).to(self.inp2lat_sacale.weight.dtype)     # the reference casts to x.dtype (:63), which only works for fp32 x
+    scale = self.lat2scale(self.inp2lat_sacale(t))
+    shift = self.lat2bias(self.inp2lat_bias(t))
     if fused:
         return cin(x, norm.weight, norm.bias, scale, shift, norm.eps)
     x = norm(x)

@@ -31,17 +31,31 @@ __device__ __forceinline__ float group_sum(float v, int gs, float* red, int slot
     return s;
 }
 
+// FiLM conditioning computed inside the forward kernel (FILM.forward, CNO_timeModule_CIN.py:62-65):
+//   scale[n,c] = lat2scale(inp2lat_sacale(t_n))_c = b2s[c] + sum_j W2s[c,j] * (w1s[j] * t_n + b1s[j]),  same for shift
+struct FilmW {
+    const float *t;                          // [N] lead times
+    const float *w1s, *b1s, *W2s, *b2s;      // scale branch: Linear(1->lat) weight[lat] / bias[lat], Linear(lat->C) weight[C,lat] / bias[C]
+    const float *w1b, *b1b, *W2b, *b2b;      // shift branch
+    float* scale_out;                        // [N,C] scale saved for backward (may be null)
+    int lat;
+};
+
 struct CinParams {
     const void* x; const void* dy; void* y;
     const float *gamma, *beta, *scale, *shift;
     float *mean, *rstd, *s1, *s2;
     int64_t planes; int c, hw, gs; float eps;
+    FilmW film;                              // film.t != nullptr: scale / shift come from the FiLM weights
 };
+
+// scale and shift of one plane, cooperatively by the `gs` threads of its group (all threads of the block must call)
+__device__ __forceinline__ void film_affine(const CinParams& p, bool live, int64_t plane, int t, int gs, float* red, float& s, float& q);
 
 template <class T, int VPT>
 __global__ void __launch_bounds__(1024) cin_fwd_reg_kernel(CinParams p) {
     constexpr int V = 16 / sizeof(T);
-    __shared__ float red[2 * 32];
+    __shared__ float red[4 * 32];
     const int gs = p.gs, ppc = blockDim.x / gs;
     const int64_t plane = (int64_t)blockIdx.x * ppc + threadIdx.x / gs;
     const int t = threadIdx.x % gs;
@@ -72,9 +86,11 @@ __global__ void __launch_bounds__(1024) cin_fwd_reg_kernel(CinParams p) {
     }
     const float var = group_sum(sq, gs, red, 1) * inv_hw;
     const float r = rsqrtf(var + p.eps);
+    float s, q;
+    if (p.film.t) film_affine(p, live, plane, t, gs, red, s, q);
     if (!live) return;
     const int ch = (int)(plane % p.c);
-    const float s = p.scale[plane], q = p.shift[plane];
+    if (!p.film.t) { s = p.scale[plane]; q = p.shift[plane]; }
     const float a = p.gamma[ch] * s * r;
     const float d0 = p.beta[ch] * s + q - mu * a;
     if (t == 0) { p.mean[plane] = mu; p.rstd[plane] = r; }
@@ -94,7 +110,7 @@ __global__ void __launch_bounds__(1024) cin_fwd_reg_kernel(CinParams p) {
 template <class T, int VPT>
 __global__ void __launch_bounds__(1024) cin_bwd_reg_kernel(CinParams p) {
     constexpr int V = 16 / sizeof(T);
-    __shared__ float red[2 * 32];
+    __shared__ float red[4 * 32];
     const int gs = p.gs, ppc = blockDim.x / gs;
     const int64_t plane = (int64_t)blockIdx.x * ppc + threadIdx.x / gs;
     const int t = threadIdx.x % gs;
@@ -145,7 +161,7 @@ __global__ void __launch_bounds__(1024) cin_bwd_reg_kernel(CinParams p) {
 // streaming path: one CTA per plane, any hw
 template <class T, bool BWD>
 __global__ void __launch_bounds__(CTA) cin_stream_kernel(CinParams p) {
-    __shared__ float red[2 * 32];
+    __shared__ float red[4 * 32];
     const int64_t plane = blockIdx.x;
     const int64_t base = plane * (int64_t)p.hw;
     const T* xp = (const T*)p.x + base;
@@ -158,8 +174,10 @@ __global__ void __launch_bounds__(CTA) cin_stream_kernel(CinParams p) {
         float sq = 0.f;
         for (int i = threadIdx.x; i < p.hw; i += CTA) { float d = to_f32(xp[i]) - mu; sq = fmaf(d, d, sq); }
         const float r = rsqrtf(group_sum(sq, CTA, red, 1) * inv_hw + p.eps);
-        const float s = p.scale[plane];
-        const float a = p.gamma[ch] * s * r, d0 = p.beta[ch] * s + p.shift[plane] - mu * a;
+        float s, q;
+        if (p.film.t) film_affine(p, true, plane, threadIdx.x, CTA, red, s, q);
+        else { s = p.scale[plane]; q = p.shift[plane]; }
+        const float a = p.gamma[ch] * s * r, d0 = p.beta[ch] * s + q - mu * a;
         if (threadIdx.x == 0) { p.mean[plane] = mu; p.rstd[plane] = r; }
         T* yp = (T*)p.y + base;
         for (int i = threadIdx.x; i < p.hw; i += CTA) yp[i] = from_f32<T>(fmaf(to_f32(xp[i]), a, d0));
@@ -176,6 +194,103 @@ __global__ void __launch_bounds__(CTA) cin_stream_kernel(CinParams p) {
             const float xh = (to_f32(xp[i]) - mu) * r;
             dp[i] = from_f32<T>(a * (to_f32(gp[i]) - m1 - xh * m2));
         }
+    }
+}
+
+__device__ __forceinline__ void film_affine(const CinParams& p, bool live, int64_t plane, int t, int gs, float* red, float& s, float& q) {
+    const FilmW& f = p.film;
+    float as = 0.f, aq = 0.f;
+    if (live) {
+        const int n = (int)(plane / p.c), ch = (int)(plane % p.c);
+        const float tn = f.t[n];
+        const float* rs = f.W2s + (int64_t)ch * f.lat; const float* rq = f.W2b + (int64_t)ch * f.lat;
+        for (int j = t; j < f.lat; j += gs) {
+            as = fmaf(rs[j], fmaf(f.w1s[j], tn, f.b1s[j]), as);
+            aq = fmaf(rq[j], fmaf(f.w1b[j], tn, f.b1b[j]), aq);
+        }
+    }
+    as = group_sum(as, gs, red, 2);
+    aq = group_sum(aq, gs, red, 3);
+    s = 0.f; q = 0.f;
+    if (live) {
+        const int ch = (int)(plane % p.c);
+        s = as + f.b2s[ch]; q = aq + f.b2b[ch];
+        if (t == 0 && f.scale_out) f.scale_out[plane] = s;
+    }
+}
+
+// ---- backward of the conditioning: every small gradient of one FILM module in ONE launch ----------------------
+//   ds = gamma*S2 + beta*S1 (d scale), dq = S1 (d shift);  per channel  P = sum_n ds*t, Q = sum_n ds, P' = sum_n dq*t, Q' = sum_n dq
+//   dgamma = sum_n scale*S2, dbeta = sum_n scale*S1, dW2s[c,j] = w1s[j]*P + b1s[j]*Q, db2s = Q, dw1s[j] = sum_c W2s[c,j]*P, db1s[j] = sum_c W2s[c,j]*Q
+// Blocks 0..nb-1 own 8 channels each; ceil(lat/32) tail blocks own the [lat] vectors (deterministic: no atomics).
+struct FilmBwd {
+    const float *s1, *s2, *t, *gamma, *beta, *scale, *w1s, *b1s, *W2s, *w1b, *b1b, *W2b;
+    float *dgamma, *dbeta, *dW2s, *db2s, *dw1s, *db1s, *dW2b, *db2b, *dw1b, *db1b;
+    int n, c, lat;
+};
+
+__device__ __forceinline__ void film_channel_sums(const FilmBwd& p, int ch, int lane, float out[6]) {
+    float dg = 0.f, db = 0.f, P = 0.f, Q = 0.f, Pq = 0.f, Qq = 0.f;
+    const float g = p.gamma[ch], b = p.beta[ch];
+    for (int n = lane; n < p.n; n += 32) {
+        const int64_t i = (int64_t)n * p.c + ch;
+        const float a1 = p.s1[i], a2 = p.s2[i], sc = p.scale[i], tn = p.t[n];
+        const float ds = fmaf(g, a2, b * a1);
+        dg = fmaf(sc, a2, dg); db = fmaf(sc, a1, db);
+        P = fmaf(ds, tn, P); Q += ds; Pq = fmaf(a1, tn, Pq); Qq += a1;
+    }
+    out[0] = warp_sum(dg); out[1] = warp_sum(db); out[2] = warp_sum(P); out[3] = warp_sum(Q); out[4] = warp_sum(Pq); out[5] = warp_sum(Qq);
+}
+
+__global__ void __launch_bounds__(256) film_bwd_finish_kernel(FilmBwd p) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nb = (p.c + 7) / 8;
+    if ((int)blockIdx.x < nb) {
+        const int ch = blockIdx.x * 8 + warp;            // one warp per channel
+        if (ch >= p.c) return;
+        float r[6];
+        film_channel_sums(p, ch, lane, r);
+        if (lane == 0) { p.dgamma[ch] = r[0]; p.dbeta[ch] = r[1]; p.db2s[ch] = r[3]; p.db2b[ch] = r[5]; }
+        for (int j = lane; j < p.lat; j += 32) {
+            p.dW2s[(int64_t)ch * p.lat + j] = fmaf(p.w1s[j], r[2], p.b1s[j] * r[3]);
+            p.dW2b[(int64_t)ch * p.lat + j] = fmaf(p.w1b[j], r[4], p.b1b[j] * r[5]);
+        }
+        return;
+    }
+    // tail blocks: dw1 / db1 of both branches = W2^T applied to the per-channel sums.  Tail block k owns 32 of the `lat`
+    // outputs; its 256 threads are 32 columns x 8 channel slices, combined through shared memory (fixed order: deterministic).
+    extern __shared__ float pq[];                          // [4][C] sums, then [8][32][4] partials
+    float* part = pq + 4 * p.c;
+    for (int ch = threadIdx.x; ch < p.c; ch += blockDim.x) {   // thread per channel, coalesced over channels
+        const float g = p.gamma[ch], b = p.beta[ch];
+        float P = 0.f, Q = 0.f, Pq = 0.f, Qq = 0.f;
+        for (int n = 0; n < p.n; n++) {
+            const float a1 = p.s1[(int64_t)n * p.c + ch], a2 = p.s2[(int64_t)n * p.c + ch], tn = p.t[n];
+            const float ds = fmaf(g, a2, b * a1);
+            P = fmaf(ds, tn, P); Q += ds; Pq = fmaf(a1, tn, Pq); Qq += a1;
+        }
+        pq[ch] = P; pq[p.c + ch] = Q; pq[2 * p.c + ch] = Pq; pq[3 * p.c + ch] = Qq;
+    }
+    __syncthreads();
+    const int jl = threadIdx.x & 31, sl = threadIdx.x >> 5;
+    const int j = ((int)blockIdx.x - nb) * 32 + jl;
+    float a = 0.f, b = 0.f, cc = 0.f, d = 0.f;
+    if (j < p.lat) {
+        const int per = (p.c + 7) / 8, c0 = sl * per, c1 = min(p.c, c0 + per);
+#pragma unroll 8
+        for (int ch = c0; ch < c1; ch++) {
+            const float ws = p.W2s[(int64_t)ch * p.lat + j], wb = p.W2b[(int64_t)ch * p.lat + j];
+            a = fmaf(ws, pq[ch], a); b = fmaf(ws, pq[p.c + ch], b);
+            cc = fmaf(wb, pq[2 * p.c + ch], cc); d = fmaf(wb, pq[3 * p.c + ch], d);
+        }
+    }
+    float* mine = part + (sl * 32 + jl) * 4;
+    mine[0] = a; mine[1] = b; mine[2] = cc; mine[3] = d;
+    __syncthreads();
+    if (sl == 0 && j < p.lat) {
+        float r[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int k = 0; k < 8; k++) for (int i = 0; i < 4; i++) r[i] += part[(k * 32 + jl) * 4 + i];
+        p.dw1s[j] = r[0]; p.db1s[j] = r[1]; p.dw1b[j] = r[2]; p.db1b[j] = r[3];
     }
 }
 
@@ -235,4 +350,33 @@ extern "C" int cno_cin_bwd(const void* x, const void* dy, void* dx, const float*
     p.mean = const_cast<float*>(mean); p.rstd = const_cast<float*>(rstd); p.s1 = s1; p.s2 = s2;
     p.planes = (int64_t)n * c; p.c = c; p.hw = hw;
     return cin_dispatch<true>(p, dtype, (cudaStream_t)stream);
+}
+
+extern "C" int cno_film_fwd(const void* x, void* y, const float* t, const float* gamma, const float* beta,
+                            const float* w1s, const float* b1s, const float* W2s, const float* b2s,
+                            const float* w1b, const float* b1b, const float* W2b, const float* b2b,
+                            float* scale_out, float* mean, float* rstd, int dtype, int n, int c, int hw, int lat,
+                            float eps, void* stream) {
+    CNO_CHECK_ARG(x && y && t && gamma && beta && w1s && b1s && W2s && b2s && w1b && b1b && W2b && b2b && mean && rstd, "film_fwd: null pointer");
+    CNO_CHECK_ARG(n >= 0 && c > 0 && hw > 0 && lat > 0, "film_fwd: bad sizes n=%d c=%d hw=%d lat=%d", n, c, hw, lat);
+    if (n == 0) return 0;
+    CinParams p{}; p.x = x; p.y = y; p.gamma = gamma; p.beta = beta; p.mean = mean; p.rstd = rstd;
+    p.planes = (int64_t)n * c; p.c = c; p.hw = hw; p.eps = eps;
+    p.film = FilmW{t, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b, scale_out, lat};
+    return cin_dispatch<false>(p, dtype, (cudaStream_t)stream);
+}
+
+extern "C" int cno_film_bwd_finish(const float* s1, const float* s2, const float* t, const float* gamma, const float* beta,
+                                   const float* scale, const float* w1s, const float* b1s, const float* W2s,
+                                   const float* w1b, const float* b1b, const float* W2b,
+                                   float* dgamma, float* dbeta, float* dW2s, float* db2s, float* dw1s, float* db1s,
+                                   float* dW2b, float* db2b, float* dw1b, float* db1b, int n, int c, int lat, void* stream) {
+    CNO_CHECK_ARG(s1 && s2 && t && gamma && beta && scale && w1s && b1s && W2s && w1b && b1b && W2b, "film_bwd_finish: null input");
+    CNO_CHECK_ARG(dgamma && dbeta && dW2s && db2s && dw1s && db1s && dW2b && db2b && dw1b && db1b, "film_bwd_finish: null output");
+    CNO_CHECK_ARG(n > 0 && c > 0 && lat > 0 && c <= 8192, "film_bwd_finish: bad sizes n=%d c=%d lat=%d", n, c, lat);
+    FilmBwd p{s1, s2, t, gamma, beta, scale, w1s, b1s, W2s, w1b, b1b, W2b, dgamma, dbeta, dW2s, db2s, dw1s, db1s, dW2b, db2b, dw1b, db1b, n, c, lat};
+    const int nb = (c + 7) / 8;
+    film_bwd_finish_kernel<<<nb + (lat + 31) / 32, 256, (size_t)(4 * c + 8 * 32 * 4) * sizeof(float), (cudaStream_t)stream>>>(p);
+    CNO_LAUNCH_CHECK();
+    return 0;
 }

@@ -60,7 +60,7 @@ class Trainer:
                                                            gradient_as_bucket_view=True, bucket_cap_mb=100, static_graph=True)
         self.opt = torch.optim.AdamW([p for p in self.model.parameters() if p.requires_grad], lr=self.model.lr,
                                      weight_decay=self.model.weight_decay, capturable=bool(graph and not ddp),
-                                     foreach=self.device.type == 'cuda')
+                                     **(dict(fused=True) if self.device.type == 'cuda' else {}))    # one multi-tensor kernel family
         self.autocast = autocast
         self.graph = None
         self.use_graph = graph and not ddp

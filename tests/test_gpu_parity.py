@@ -309,6 +309,34 @@ def test_cin_golden(cno, golden, name):
         assert rel(gr, T(g[f'{name}.g.{n}'])) < 5e-5, n
 
 
+@pytest.mark.parametrize('fuse', [True, False])
+@pytest.mark.parametrize('N,C,S,dtype', [(32, 256, 8, torch.float32), (4, 16, 128, torch.float32), (3, 40, 16, torch.float32),
+                                         (2, 8, 256, torch.float32), (5, 7, 10, torch.float32), (8, 64, 32, torch.bfloat16)])
+def test_film_module_fused_vs_eager(cno, N, C, S, dtype, fuse, monkeypatch):
+    """whole FILM module (4 Linear + instance norm + affine): fused kernels vs the module's eager torch ops on CPU,
+    all eleven gradients (FILM.forward, CNO_timeModule_CIN.py:60-70)."""
+    from pregenerating_pde_b200 import cno_model
+    monkeypatch.setattr(cno.cin, 'FUSE_LINEARS', fuse)
+    torch.manual_seed(N * 100 + C)
+    m = cno_model.FILM(C, dim=[2, 3], s=S)
+    with torch.no_grad():
+        for p_ in m.parameters():
+            p_.add_(0.3 * torch.randn_like(p_))
+    x = (torch.randn(N, C, S, S) * 1.3 + 0.2).to(dtype).float(); t = torch.rand(N); dy = torch.randn(N, C, S, S).to(dtype).float()
+    xr = x.clone().requires_grad_(True)
+    y_ref = m(xr, t)                                   # CPU tensors -> the module's own torch ops
+    g_ref = torch.autograd.grad(y_ref, [xr] + list(m.parameters()), dy)
+    import copy
+    mg = copy.deepcopy(m).to(DEV)
+    xg = x.to(DEV, dtype).requires_grad_(True)
+    y = mg(xg, t.to(DEV))
+    g_got = torch.autograd.grad(y, [xg] + list(mg.parameters()), dy.to(DEV, dtype))
+    tol = 2e-5 if dtype == torch.float32 else 2e-2
+    assert y.dtype == dtype and rel(y, y_ref) < tol
+    for (n_, _), a, r in zip([('x', None)] + list(m.named_parameters()), g_got, g_ref):
+        assert rel(a, r) < (1e-4 if dtype == torch.float32 else 4e-2), n_
+
+
 @pytest.mark.parametrize('N,C,S', [(32, 16, 128), (8, 32, 64), (4, 64, 32), (4, 128, 16), (4, 256, 8), (1, 2, 256), (2, 3, 10)])
 @pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
 def test_cin_sizes(cno, N, C, S, dtype):
