@@ -49,6 +49,15 @@ FLR_DEV f2 ffma2(f2 a, f2 b, f2 c) {
 #endif
 }
 
+// (hi:lo) << s, upper word  (SHF.L.W on the device)
+FLR_DEV uint32_t funnel_l(uint32_t lo, uint32_t hi, int s) {
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_l(lo, hi, s);
+#else
+    return (hi << s) | (lo >> (32 - s));
+#endif
+}
+
 FLR_DEV uint32_t f_bits(float v) {
 #if defined(__CUDA_ARCH__)
     return __float_as_uint(v);
@@ -64,7 +73,20 @@ template <class T> struct Cvt;
 template <> struct Cvt<float> { static FLR_DEV float get(float v) { return v; } };
 
 
-constexpr int NSTAGE = 3;
+// build-time tunables (defaults = the shipped configuration; tools/variants.sh builds others for A/B timing)
+#ifndef FLR_NSTAGE
+#define FLR_NSTAGE 3
+#endif
+#ifndef FLR_MAXT
+#define FLR_MAXT 256            // threads per CTA (launch bound)
+#endif
+#ifndef FLR_MINB
+#define FLR_MINB 2              // resident CTAs per SM the register budget is sized for
+#endif
+#ifndef FLR_SMEM_KB
+#define FLR_SMEM_KB 100         // shared memory budget per CTA
+#endif
+constexpr int NSTAGE = FLR_NSTAGE;
 
 // Everything the kernel needs besides the tensor map.  Filled by the host (flrelu_fused.cu).
 struct Params {
@@ -80,7 +102,10 @@ struct Params {
     int tmaX, xshift;          // TMA start column = cminX rounded down to a 16-byte boundary (the hardware faults on an
                                // unaligned innermost coordinate; measured, tools/probes/tma_probe.cu); xshift = cminX - tmaX
     int bwx;                   // x tile row pitch (elements) = TMA box width
-    int dp;                    // D row pitch in floats (multiple of 32)
+    int dp, dq;                // D row pitch in floats = 4 * DOWN * dq.  A finished row is stored as DOWN interleaved classes:
+                               // float4 f sits at float4 position (f / DOWN) + (f % DOWN) * dq, dq = 8 / DOWN (mod 8), so that the
+                               // writers (consecutive f) and the h-down readers (f = DOWN*cq + i) are both bank-conflict free and
+                               // a reader's NF4 loads are constant offsets from one address
     int ncq, ncq_shift;        // output column quads per row = ceil(OW/4); log2 when a power of two, else -1
     int stage_bytes;           // bytes of one x stage (multiple of 128)
     int mask_h, mask_w, mask_pitch, sx, sy;
@@ -143,7 +168,7 @@ FLR_DEV CtaGeom seg_geom(const Params& p, int gr, int r1) {
     return g;
 }
 
-FLR_DEV int swz(int f4idx) { return f4idx ^ ((f4idx >> 3) & 7); }
+template <class C> FLR_DEV int dpos(const Params& p, int f4idx) { return f4idx / C::DOWN + (f4idx % C::DOWN) * p.dq; }
 
 // ------------------------------------------------------------------------------------------------
 // per-thread state of the streaming phase (lives in registers on the device)
@@ -154,6 +179,7 @@ struct Stream {
     f2 acc[C::ND][2];       // rotating output-row accumulators of the vertical down-FIR
     f2 bE[2];               // bias times the horizontal edge profile of the up-FIR
     int unit, g;            // plane slot in the CTA, column group
+    int dofs;               // float offset of this thread's float4 inside a D row
     bool active;
     uint32_t colmask;       // WRITE: valid-column bits; READ: valid mask-element bits
     int rd_byte, rd_shift;  // READ: first mask byte of this thread, bit shift
@@ -162,6 +188,7 @@ struct Stream {
     template <class LD>
     FLR_DEV void init(const Params& p, const CtaGeom& cg, int tid, LD ld_bias) {
         unit = tid / p.G; g = tid - unit * p.G;
+        dofs = 4 * dpos<C>(p, g);
         const int plane = cg.plane0 + unit;
         active = unit < p.P && plane < p.NC;
         FLR_UNROLL for (int r = 0; r < C::ND; r++) { acc[r][0] = mk2(0.f, 0.f); acc[r][1] = mk2(0.f, 0.f); }
@@ -182,7 +209,7 @@ struct Stream {
             bE[pr] = mk2(e0 * bias, e1 * bias);
         }
         if (MODE == SIGN_WRITE) {
-            FLR_UNROLL for (int m = 0; m < 4; m++) if (4 * g + m < p.UW) colmask |= 3u << (2 * m);
+            FLR_UNROLL for (int m = 0; m < 4; m++) if (4 * g + m < p.UW) colmask |= 1u << (2 * m);   // bit 0 of each 2-bit code
             mrow0 = p.mask + (int64_t)plane * p.mask_h * p.mask_pitch + g;
         } else if (MODE == SIGN_READ) {
             const int e0 = 4 * g + p.sx;
@@ -199,13 +226,12 @@ struct Stream {
         const int xoff = ((C::UP == 2) ? 2 * g : g) + p.xshift;
 #if defined(__CUDA_ARCH__)
         if (C::UP == 2 && sizeof(T) == 4) {          // LDS.64 from the even column at or below xoff
-            const float2* src = reinterpret_cast<const float2*>(xrow + (xoff & ~1));
-            if (xoff & 1) {                          // uniform branch (xshift is a launch constant)
-                float t[10];
-                FLR_UNROLL for (int w = 0; w < 5; w++) { const float2 v = src[w]; t[2 * w] = v.x; t[2 * w + 1] = v.y; }
-                FLR_UNROLL for (int w = 0; w < 8; w++) xs[w] = t[w + 1];
+            if (xoff & 1) {                          // uniform branch (xshift is a launch constant): LDS.32, 3 x LDS.64, LDS.32
+                xs[0] = xrow[xoff];
+                FLR_UNROLL for (int w = 0; w < 3; w++) { const float2 v = *reinterpret_cast<const float2*>(xrow + xoff + 1 + 2 * w); xs[1 + 2 * w] = v.x; xs[2 + 2 * w] = v.y; }
+                xs[7] = xrow[xoff + 7];
             } else {
-                FLR_UNROLL for (int w = 0; w < 4; w++) { const float2 v = src[w]; xs[2 * w] = v.x; xs[2 * w + 1] = v.y; }
+                FLR_UNROLL for (int w = 0; w < 4; w++) { const float2 v = *reinterpret_cast<const float2*>(xrow + xoff + 2 * w); xs[2 * w] = v.x; xs[2 * w + 1] = v.y; }
             }
         } else
 #endif
@@ -239,8 +265,10 @@ struct Stream {
             v[0] = ffma2(v[0], mk2(m[0], m[1]), z); v[1] = ffma2(v[1], mk2(m[2], m[3]), z);
         } else {
             if (MODE == SIGN_WRITE) {
-                const uint32_t u0 = f_bits(v[0].x), u1 = f_bits(v[0].y), u2 = f_bits(v[1].x), u3 = f_bits(v[1].y);
-                code = ((u0 >> 31) | ((u1 >> 29) & 4u) | ((u2 >> 27) & 16u) | ((u3 >> 25) & 64u)) & colmask;
+                // sign bits of four floats -> bits 0, 2, 4, 6: one shift + three funnel shifts + shift + and
+                uint32_t r = f_bits(v[1].y) >> 30;
+                r = funnel_l(f_bits(v[1].x), r, 2); r = funnel_l(f_bits(v[0].y), r, 2); r = funnel_l(f_bits(v[0].x), r, 2);
+                code = (r >> 1) & colmask;
             }
             // lrelu(v) = max(v, slope*v); the host plan only admits 0 <= slope <= 1
             const f2 sl = mk2(p.slope, p.slope), z = mk2(0.f, 0.f);
@@ -281,7 +309,11 @@ struct Stream {
                 v[1] = ffma2(win[(phi > C::RY ? 1 : 0) + k][1], t, v[1]);
             }
             act(p, v, code);
+#ifndef FLR_X_NOMASK
             if (MODE == SIGN_WRITE) { if (j < p.UH) mrow0[(int64_t)j * p.mask_pitch] = (uint8_t)code; }
+#else
+            if (MODE == SIGN_WRITE) { if (j < p.UH && code == 0x12345u) mrow0[(int64_t)j * p.mask_pitch] = (uint8_t)code; }
+#endif
             // vertical down-FIR, scatter form: row r of this body completes at jl = DOWN*r + DOWN-1
             FLR_UNROLL for (int r = 0; r < C::ND; r++) {
                 const int t = (jl <= C::DOWN * r + C::DOWN - 1) ? jl + C::DOWN * (C::ND - 1 - r) : jl - C::DOWN * (r + 1);
@@ -292,7 +324,7 @@ struct Stream {
             if (jl % C::DOWN == C::DOWN - 1) {
                 const int r = jl / C::DOWN;
                 f4 o; o.x = acc[r][0].x; o.y = acc[r][0].y; o.z = acc[r][1].x; o.w = acc[r][1].y;
-                reinterpret_cast<f4*>(Dbuf + r * p.dp)[swz(g)] = o;
+                *reinterpret_cast<f4*>(Dbuf + r * p.dp + dofs) = o;
                 acc[r][0] = mk2(0.f, 0.f); acc[r][1] = mk2(0.f, 0.f);
             }
         }
@@ -335,21 +367,21 @@ FLR_DEV void hdown_phase(const Params& p, const CtaGeom& cg, int tid, int nthrea
                          const float* Dbuf /* [P][KO][dp] */, ST store4) {
     const int o_base = cg.o0 - (C::ND - 1) + body_idx * C::KO;
     const int ntask = p.P * C::KO * p.ncq;
+    const unsigned nrows_ok = (unsigned)(cg.o1 - cg.o0);
     for (int task = tid; task < ntask; task += nthreads) {
-        int cq, t2;
+        int cq, t2;                                            // t2 = unit * KO + row: D rows are contiguous in that order
         if (p.ncq_shift >= 0) { cq = task & (p.ncq - 1); t2 = task >> p.ncq_shift; }
         else { t2 = task / p.ncq; cq = task - t2 * p.ncq; }
-        const int r = t2 % C::KO, u = t2 / C::KO;
+        const int u = t2 / C::KO, r = t2 - u * C::KO;
         const int o = o_base + r, plane = cg.plane0 + u;
-        if (o < cg.o0 || o >= cg.o1 || plane >= p.NC) continue;
-        const f4* drow = reinterpret_cast<const f4*>(Dbuf + (u * C::KO + r) * p.dp);
+        if ((unsigned)(o - cg.o0) >= nrows_ok || plane >= p.NC) continue;
+        const f4* drow = reinterpret_cast<const f4*>(Dbuf + t2 * p.dp) + cq;
         f4 d[C::NF4];
-        FLR_UNROLL for (int i = 0; i < C::NF4; i++) d[i] = drow[swz(C::DOWN * cq + i)];
+        FLR_UNROLL for (int i = 0; i < C::NF4; i++) d[i] = drow[(i / C::DOWN) + (i % C::DOWN) * p.dq];
         float out[4];
         FLR_UNROLL for (int i = 0; i < 4; i++) {
             f2 a = mk2(0.f, 0.f);
-            FLR_UNROLL for (int m = 0; m < C::TD / 2; m++)
-                {
+            FLR_UNROLL for (int m = 0; m < C::TD / 2; m++) {
                 const int e = C::DOWN * i + 2 * m;     // even: both lanes sit in the same float4
                 a = ffma2(mk2(f4c(d[e >> 2], e & 3), f4c(d[e >> 2], (e & 3) + 1)), mk2(p.fd[2 * m], p.fd[2 * m + 1]), a);
             }

@@ -55,7 +55,7 @@ template <> __device__ __forceinline__ void store_quad<__half>(__half* dst, cons
 }
 
 template <class T, class C, int MODE>
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(FLR_MAXT, FLR_MINB)
 flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ Params p) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* xst = smem;
@@ -123,7 +123,9 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 const int consumed = 1 + (k + 1) / C::M;
                 while (next_load < cg.nstages_total && next_load < consumed + NSTAGE) issue(next_load++);
             }
+#ifndef FLR_X_NOHDOWN
             hdown_phase<T, C>(p, cg, tid, blockDim.x, k, D + (size_t)(k & 1) * p.P * C::KO * p.dp, store4);
+#endif
         }
         gs0 += cg.nstages_total;
         gr += cg.o1 - cg.o0;

@@ -74,7 +74,7 @@ static inline int make_plan(Plan& plan, int elem_size, int n, int c, int in_h, i
     p.UW = out_w * down - (down - 1) + (fd_taps - 1);
     p.G = (p.UW + 15) / 16 * 4;          // one thread per mask byte, mask rows padded to 16 elements
                                          // (filtered_lrelu.cpp:83-85): the pad bytes are written as zeros
-    if (p.G > 256) return -1;
+    if (p.G > FLR_MAXT) return -1;
     p.cminX = -floor_div_i(px0, up);
     p.cminY = -floor_div_i(py0, up);
     const int epv = 16 / elem_size;                                    // elements per 16 bytes
@@ -84,24 +84,31 @@ static inline int make_plan(Plan& plan, int elem_size, int n, int c, int in_h, i
     bwx = (bwx + epv - 1) / epv * epv;
     if (bwx > 256) return -1;                                          // TMA box limit
     p.bwx = bwx;
-    p.dp = ((4 * p.G > down * 4 * ((out_w + 3) / 4) + 6 * down ? 4 * p.G : down * 4 * ((out_w + 3) / 4) + 6 * down) + 31) / 32 * 32;
     p.ncq = (out_w + 3) / 4;
+    {   // D row layout (flrelu_core.h Params::dq): DOWN classes of dq float4 each
+        const int nf4 = (down * 3 + 6 * down + 3) / 4;                 // float4 loads of one h-down task (Cfg::NF4)
+        int q = (p.G + down - 1) / down;
+        const int need = p.ncq + (nf4 - 1) / down + 1;
+        if (q < need) q = need;
+        while (q % 8 != 8 / down) q++;
+        p.dq = q; p.dp = 4 * down * q;
+    }
     p.ncq_shift = -1;
     for (int s = 0; s < 16; s++) if ((1 << s) == p.ncq) p.ncq_shift = s;
     const int rs = variant_rs(up, down, ry);
     const int mstride = ((p.G + 4 + 3) / 4) * 4;                      // staged mask row (READ mode): G + 1 bytes at any 4-byte phase
     p.mstride = mstride; p.mnw = mstride / 4; p.mws = 0;
     // planes per CTA: fill up to 256 threads, stay inside ~100 KB of shared memory (2 CTAs / SM)
-    int P = 256 / p.G; if (P < 1) P = 1; if (P > p.NC) P = p.NC;
+    int P = FLR_MAXT / p.G; if (P < 1) P = 1; if (P > p.NC) P = p.NC;
     for (;; P--) {
         const size_t stage = ((size_t)P * rs * bwx * elem_size + 127) / 128 * 128;
         const size_t total = NSTAGE * stage + (size_t)2 * P * 6 * p.dp * 4 + 64 + (size_t)2 * P * (6 * down) * mstride;
-        if (total <= 100 * 1024 || P == 1) { p.stage_bytes = (int)stage; plan.smem_bytes = total; break; }
+        if (total <= FLR_SMEM_KB * 1024 || P == 1) { p.stage_bytes = (int)stage; plan.smem_bytes = total; break; }
     }
     if (plan.smem_bytes > 220 * 1024) return -1;
     p.P = P;
     plan.threads = (P * p.G + 31) / 32 * 32;
-    if (plan.threads > 256) { /* G > 256/P cannot happen */ return -1; }
+    if (plan.threads > FLR_MAXT) return -1;
     // persistent CTAs over the global row space (flrelu_core.h cta_cut); finalised by set_partition()
     p.rows_total = ((p.NC + P - 1) / P) * out_h;
     set_partition(plan, forced_ctas > 0 ? forced_ctas : 2 * 148, forced_ctas > 0);
