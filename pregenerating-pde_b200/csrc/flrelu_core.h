@@ -75,18 +75,19 @@ template <> struct Cvt<float> { static FLR_DEV float get(float v) { return v; } 
 
 // build-time tunables (defaults = the shipped configuration; tools/variants.sh builds others for A/B timing)
 #ifndef FLR_NSTAGE
-#define FLR_NSTAGE 3
+#define FLR_NSTAGE 2
 #endif
 #ifndef FLR_MAXT
-#define FLR_MAXT 256            // threads per CTA (launch bound)
+#define FLR_MAXT 512            // threads per CTA (launch bound)
 #endif
 #ifndef FLR_MINB
-#define FLR_MINB 2              // resident CTAs per SM the register budget is sized for
+#define FLR_MINB 1              // resident CTAs per SM the register budget is sized for
 #endif
 #ifndef FLR_SMEM_KB
-#define FLR_SMEM_KB 100         // shared memory budget per CTA
+#define FLR_SMEM_KB 212         // shared memory budget per CTA
 #endif
 constexpr int NSTAGE = FLR_NSTAGE;
+constexpr int NDBUF = 3;           // D buffers (finished v-down rows) in flight, see flr_fused_kernel
 
 // Everything the kernel needs besides the tensor map.  Filled by the host (flrelu_fused.cu).
 struct Params {

@@ -54,13 +54,25 @@ template <> __device__ __forceinline__ void store_quad<__half>(__half* dst, cons
     *reinterpret_cast<uint2*>(dst) = u;
 }
 
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// Synchronisation inside a CTA (no __syncthreads in the steady state):
+//   x stages   : NSTAGE-slot TMA ring, one mbarrier per slot (transaction bytes)
+//   D buffers  : NDBUF = 3 buffers of finished v-down rows.  Body k writes D[k % 3] and every thread arrives on full[k % 3];
+//                the h-down of body k-1 runs AFTER body k, so its wait on full[k-1] has had a whole body to complete, and the
+//                wait in front of body k+1 (guard for reusing D[(k+1) % 3] and the x slot / mask buffer of body k) comes after
+//                that h-down work.  Warps therefore drift by up to one h-down phase without stalling each other.
 template <class T, class C, int MODE>
 __global__ void __launch_bounds__(FLR_MAXT, FLR_MINB)
 flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ Params p) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* xst = smem;
     float* D = reinterpret_cast<float*>(smem + (size_t)NSTAGE * p.stage_bytes);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(D + (size_t)2 * p.P * C::KO * p.dp);
+    const size_t dbuf = (size_t)p.P * C::KO * p.dp;                      // floats per D buffer
+    uint64_t* bars = reinterpret_cast<uint64_t*>(D + NDBUF * dbuf);
+    uint64_t* full = bars + NSTAGE;
     uint8_t* M = reinterpret_cast<uint8_t*>(bars) + 64;                 // READ: 2 x [P][PB][mstride] staged mask rows
     const size_t mbuf = (size_t)p.P * C::PB * p.mstride;
     auto copy4 = [](uint8_t* dst, const uint8_t* src, bool ok) {
@@ -71,6 +83,7 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 
     if (tid == 0) {
         for (int i = 0; i < NSTAGE; i++) mbar_init(&bars[i], 1);
+        for (int i = 0; i < NDBUF; i++) mbar_init(&full[i], blockDim.x);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -88,9 +101,10 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     // this CTA's range of the global row space, processed segment by segment
     const int r0 = cta_cut(p, blockIdx.x, C::ALIGN, C::SNAP), r1 = cta_cut(p, blockIdx.x + 1, C::ALIGN, C::SNAP);
     int gs0 = 0;                                  // x stages issued by earlier segments (slot / parity bookkeeping)
+    int db = 0; uint32_t dpar = 0;                // D buffer / full-barrier slot and phase parity of the NEXT body
     for (int gr = r0; gr < r1;) {
         const CtaGeom cg = seg_geom<C>(p, gr, r1);
-        __syncthreads();                          // barrier init visible; previous segment's D buffers and x stages are free
+        __syncthreads();                          // barrier init visible; the previous segment is completely finished
         int next_load = 0;
         auto issue = [&](int s) {
             const int slot = (gs0 + s) % NSTAGE;
@@ -107,26 +121,32 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         if (st.active) st.prologue(p, reinterpret_cast<const T*>(xst + (size_t)(gs0 % NSTAGE) * p.stage_bytes) + (size_t)st.unit * C::RS * p.bwx, cg.row0);
         if (MODE == SIGN_READ) { asm volatile("cp.async.wait_all;" ::: "memory"); __syncthreads(); }
 
+        int pb = 0; uint32_t ppar = 0;            // slot / parity of the previous body
         for (int k = 0; k < cg.nbodies; k++) {
             const int s = 1 + k / C::M, slot = (gs0 + s) % NSTAGE, sub = k % C::M;
+            if (k > 0) {
+                mbar_wait(&full[pb], ppar);       // every thread has finished body k-1 (and the h-down of body k-3)
+                if (tid == 0) {
+                    const int consumed = 1 + k / C::M;
+                    while (next_load < cg.nstages_total && next_load < consumed + NSTAGE) issue(next_load++);
+                }
+            }
             if (MODE == SIGN_READ && k + 1 < cg.nbodies)                 // next body's mask rows, in flight during this body
                 stage_mask<C>(p, cg, cg.j_b0 + (k + 1) * C::PB, tid, blockDim.x, M + (size_t)((k + 1) & 1) * mbuf, copy4);
             if (sub == 0) mbar_wait(&bars[slot], (uint32_t)(((gs0 + s) / NSTAGE) & 1));
             if (st.active)
                 st.body(p, reinterpret_cast<const T*>(xst + (size_t)slot * p.stage_bytes) + ((size_t)st.unit * C::RS + sub * C::PQ) * p.bwx,
                         cg.row0 + s * C::RS + sub * C::PQ, cg.j_b0 + k * C::PB,
-                        D + ((size_t)(k & 1) * p.P + st.unit) * C::KO * p.dp,
+                        D + db * dbuf + (size_t)st.unit * C::KO * p.dp,
                         M + (size_t)(k & 1) * mbuf + (size_t)st.unit * C::PB * p.mstride);
             if (MODE == SIGN_READ) asm volatile("cp.async.wait_all;" ::: "memory");
-            __syncthreads();
-            if (tid == 0) {
-                const int consumed = 1 + (k + 1) / C::M;
-                while (next_load < cg.nstages_total && next_load < consumed + NSTAGE) issue(next_load++);
-            }
-#ifndef FLR_X_NOHDOWN
-            hdown_phase<T, C>(p, cg, tid, blockDim.x, k, D + (size_t)(k & 1) * p.P * C::KO * p.dp, store4);
-#endif
+            mbar_arrive(&full[db]);
+            if (k > 0) hdown_phase<T, C>(p, cg, tid, blockDim.x, k - 1, D + pb * dbuf, store4);
+            pb = db; ppar = dpar;
+            if (++db == NDBUF) { db = 0; dpar ^= 1u; }
         }
+        mbar_wait(&full[pb], ppar);               // drain: h-down of the segment's last body
+        hdown_phase<T, C>(p, cg, tid, blockDim.x, cg.nbodies - 1, D + pb * dbuf, store4);
         gs0 += cg.nstages_total;
         gr += cg.o1 - cg.o0;
     }

@@ -98,14 +98,14 @@ static inline int make_plan(Plan& plan, int elem_size, int n, int c, int in_h, i
     const int rs = variant_rs(up, down, ry);
     const int mstride = ((p.G + 4 + 3) / 4) * 4;                      // staged mask row (READ mode): G + 1 bytes at any 4-byte phase
     p.mstride = mstride; p.mnw = mstride / 4; p.mws = 0;
-    // planes per CTA: fill up to 256 threads, stay inside ~100 KB of shared memory (2 CTAs / SM)
+    // planes per CTA: fill up to FLR_MAXT threads (one big CTA per SM balances the four schedulers best), stay inside FLR_SMEM_KB
     int P = FLR_MAXT / p.G; if (P < 1) P = 1; if (P > p.NC) P = p.NC;
     for (;; P--) {
         const size_t stage = ((size_t)P * rs * bwx * elem_size + 127) / 128 * 128;
-        const size_t total = NSTAGE * stage + (size_t)2 * P * 6 * p.dp * 4 + 64 + (size_t)2 * P * (6 * down) * mstride;
+        const size_t total = NSTAGE * stage + (size_t)NDBUF * P * 6 * p.dp * 4 + 64 + (size_t)2 * P * (6 * down) * mstride;
         if (total <= FLR_SMEM_KB * 1024 || P == 1) { p.stage_bytes = (int)stage; plan.smem_bytes = total; break; }
     }
-    if (plan.smem_bytes > 220 * 1024) return -1;
+    if (plan.smem_bytes > 227 * 1024) return -1;
     p.P = P;
     plan.threads = (P * p.G + 31) / 32 * 32;
     if (plan.threads > FLR_MAXT) return -1;
