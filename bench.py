@@ -248,7 +248,7 @@ def run_cno_train(args):
         dist.init_process_group('nccl', device_id=dev)
     torch.backends.cudnn.benchmark = True
     B = args.batch
-    tr = cno.train.Trainer(device=dev, ddp=world > 1, graph=args.graph and world == 1)
+    tr = cno.train.Trainer(device=dev, ddp=world > 1, graph=bool(args.graph))
     batches = [cno.train.synthetic_fpo_batch(B, device='cpu', seed=100 * rank + i) for i in range(2)]
     host = [tuple(v.pin_memory() for v in b) for b in batches]
     devb = [tuple(v.to(dev) for v in b) for b in batches]
@@ -286,7 +286,7 @@ def run_cno_train(args):
             'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': round(ms, 3), 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
             'config': {'workload': 'CNO_time TrainCNO_time_L config (N_layers 4, N_res 8, 18.28M params) fwd + rel-L1 + bwd + AdamW, FPO 7ch 128x128',
-                       'batch_per_gpu': B, 'cuda_graph': bool(tr.use_graph), 'parallelism': f'dp{world}', 'final_loss': round(float(loss), 5)},
+                       'batch_per_gpu': B, 'cuda_graph': bool(tr.use_graph), 'parallelism': f'dp{world}', 'grad_allreduce': tr.dp_mode, 'final_loss': round(float(loss), 5)},
             'e2e': {'value': round(world * B / (e2e_ms * 1e-3), 2), 'unit': 'samples/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 4,
                     'ms_per_step': round(e2e_ms, 3)},
             'clocks': clocks}))

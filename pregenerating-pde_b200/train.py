@@ -54,16 +54,28 @@ class Trainer:
         self.model = cno_model.CNO_time(**cfg).to(self.device)
         freeze_dead_parameters(self.model)
         self.net = self.model
+        self.world = dist.get_world_size() if (ddp and dist.is_initialized()) else 1
+        # data parallelism, two flavours with identical numerics (mean of the per-rank gradients):
+        #  'ddp'  : torch DistributedDataParallel (bucketed all-reduce overlapped with backward), eager launches
+        #  'flat' : one NCCL all-reduce of the flattened gradients after backward; capturable, so the whole step
+        #           (forward, backward, all-reduce, AdamW) replays as ONE CUDA graph per rank
+        self.dp_mode = None
         if ddp:
+            self.dp_mode = 'flat' if (graph and self.device.type == 'cuda') else 'ddp'
+        if self.dp_mode == 'ddp':
             self.net = nn.parallel.DistributedDataParallel(self.model, device_ids=[self.device.index] if self.device.type == 'cuda' else None,
                                                            broadcast_buffers=False,
                                                            gradient_as_bucket_view=True, bucket_cap_mb=100, static_graph=True)
+        elif self.dp_mode == 'flat':
+            with torch.no_grad():                      # same start on every rank (DDP does this broadcast itself)
+                for p in self.model.parameters():
+                    dist.broadcast(p, 0)
         self.opt = torch.optim.AdamW([p for p in self.model.parameters() if p.requires_grad], lr=self.model.lr,
-                                     weight_decay=self.model.weight_decay, capturable=bool(graph and not ddp),
+                                     weight_decay=self.model.weight_decay, capturable=bool(graph and self.dp_mode != 'ddp'),
                                      **(dict(fused=True) if self.device.type == 'cuda' else {}))    # one multi-tensor kernel family
         self.autocast = autocast
         self.graph = None
-        self.use_graph = graph and not ddp
+        self.use_graph = bool(graph) and self.dp_mode != 'ddp' and self.device.type == 'cuda'
         self.static = None
 
     def _step_eager(self, t, x, y):
@@ -72,8 +84,17 @@ class Trainer:
             pred = self.net(x, t)
         loss = self.model.training_loss(pred.float(), y.float())
         loss.backward()
+        if self.dp_mode == 'flat':
+            self._allreduce_flat()
         self.opt.step()
         return loss.detach()
+
+    def _allreduce_flat(self):
+        grads = [p.grad for p in self.model.parameters() if p.grad is not None]
+        flat = torch.cat([g.reshape(-1) for g in grads])
+        dist.all_reduce(flat)
+        flat.mul_(1.0 / self.world)
+        torch._foreach_copy_(grads, [c.view_as(g) for c, g in zip(flat.split([g.numel() for g in grads]), grads)])
 
     def step(self, t, x, y):
         if not self.use_graph:
