@@ -75,9 +75,16 @@ __global__ void __launch_bounds__(256) bias_act_kernel(BAParams p) {
         if (xr) vxr = ld16_stream(xr + i0);
         if (yr) vyr = ld16_stream(yr + i0);
         if (dyp) vdy = ld16_stream(dyp + i0);
+        // bias index: one 32-bit division per 16-byte vector when the whole vector lies in one bias run (step_b % V == 0,
+        // the NCHW case); per element otherwise (channels_last: step_b == 1)
+        const bool need_b = b != nullptr && (GRAD == 0 || ACT == 9);      // only swish reads x + b again in its gradients
+        const uint32_t sb = (uint32_t)p.step_b, nb = (uint32_t)p.size_b;
+        const bool uni = (sb % V) == 0;
+        S bvec = (S)0;
+        if (need_b && uni) bvec = ldc(b[((uint32_t)i0 / sb) % nb]);
 #pragma unroll
         for (int k = 0; k < V; k++) {
-            S bb = b ? ldc(b[((i0 + k) / p.step_b) % p.size_b]) : (S)0;
+            S bb = need_b ? (uni ? bvec : ldc(b[(((uint32_t)i0 + k) / sb) % nb])) : (S)0;
             vo.v[k] = stc<T, S>(one(ldc(vx.v[k]), bb, xr ? ldc(vxr.v[k]) : (S)0, yr ? ldc(vyr.v[k]) : (S)0, dyp ? ldc(vdy.v[k]) : (S)1));
         }
         st16(y + i0, vo);
@@ -126,6 +133,7 @@ extern "C" int cno_bias_act(const void* x, const void* b, const void* xref, cons
     CNO_CHECK_ARG(dtype >= CNO_F32 && dtype <= CNO_F64, "bias_act: bad dtype %d", dtype);
     CNO_CHECK_ARG(!b || (size_b > 0 && step_b > 0), "bias_act: bias needs size_b, step_b > 0");
     if (numel <= 0) return 0;
+    CNO_CHECK_ARG(numel <= 0x7fffffffll, "bias_act: x is too large");      // 32-bit index maths (bias_act.cpp:37)
     const int es = cno_dtype_size(dtype);
     auto mis = [&](const void* q) { return q && ((uintptr_t)q & 15u); };
     CNO_CHECK_ARG(!(mis(x) || mis(xref) || mis(yref) || mis(dy) || mis(y)),

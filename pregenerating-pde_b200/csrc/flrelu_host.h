@@ -39,7 +39,8 @@ static inline bool variant_compiled(int up, int down, int rx, int ry) {
 // number of persistent CTAs: every resident slot, but at least two bodies of output rows per CTA
 static inline void set_partition(Plan& plan, int max_ctas, bool forced = false) {
     Params& p = plan.p;
-    int n = forced ? max_ctas : p.rows_total / 12;
+    const int min_rows = p.OH < 12 ? p.OH : 12;            // at least two bodies of output rows (or one short plane) per CTA
+    int n = forced ? max_ctas : p.rows_total / min_rows;
     if (n > max_ctas) n = max_ctas;
     if (n > p.rows_total) n = p.rows_total;
     if (n < 1) n = 1;
@@ -100,6 +101,15 @@ static inline int make_plan(Plan& plan, int elem_size, int n, int c, int in_h, i
     p.mstride = mstride; p.mnw = mstride / 4; p.mws = 0;
     // planes per CTA: fill up to FLR_MAXT threads (one big CTA per SM balances the four schedulers best), stay inside FLR_SMEM_KB
     int P = FLR_MAXT / p.G; if (P < 1) P = 1; if (P > p.NC) P = p.NC;
+    {   // widest CTA (best scheduler balance, fewest wasted lanes) that still cuts the global row space into at least two
+        // CTA-sized ranges per SM; short planes end up with fewer planes per CTA, i.e. more, smaller, concurrent CTAs
+        static int forced = -1;
+        if (forced < 0) { const char* e = getenv("CNO_FLR_P"); forced = e ? atoi(e) : 0; }
+        const int p_min = (128 + p.G - 1) / p.G;
+        const int min_rows = out_h < 12 ? out_h : 12;
+        while (P > p_min && (int64_t)((p.NC + P - 1) / P) * out_h / min_rows < 2 * 148) P--;
+        if (forced > 0 && forced < P) P = forced;
+    }
     for (;; P--) {
         const size_t stage = ((size_t)P * rs * bwx * elem_size + 127) / 128 * 128;
         const size_t total = NSTAGE * stage + (size_t)NDBUF * P * 6 * p.dp * 4 + 64 + (size_t)2 * P * (6 * down) * mstride;
