@@ -30,7 +30,35 @@ def _rel(a, b):
     return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
 
 
-def _check(golden, dev, tol):
+def _eager_film(self, x, t):
+    """FILM.forward in plain torch ops (CNO_timeModule_CIN.py:60-70)"""
+    t = t.reshape(-1, 1).to(x.dtype)
+    s, q = self.lat2scale(self.inp2lat_sacale(t)), self.lat2bias(self.inp2lat_bias(t))
+    return self.norm(x) * s[:, :, None, None] + q[:, :, None, None]
+
+
+def _torch_backend_deviation(golden, dev):
+    """gradients of the same checkpoint on `dev` with torch ops only (impl='ref' LReLu, eager FILM): their distance to the CPU
+    golden gradients is what the device's convolution backend alone contributes (none of our kernels runs)."""
+    from pregenerating_pde_b200 import cno_model
+    g, sd = _load(golden)
+    model = _build(dev)
+    model.load_state_dict(sd, strict=True)
+    for m in model.modules():
+        if isinstance(m, cno_model.LReLu):
+            m.impl = 'ref'
+    fused = cno_model.FILM.forward
+    cno_model.FILM.forward = _eager_film
+    try:
+        x, t, target = (torch.from_numpy(g[k]).to(dev) for k in ('x', 't', 'target'))
+        model.training_loss(model(x, t), target).backward()
+    finally:
+        cno_model.FILM.forward = fused
+    named = dict(model.named_parameters())
+    return {k: _rel(named[k[5:]].grad, g[k]) for k in g.files if k.startswith('grad.')}
+
+
+def _check(golden, dev, tol, backend_dev=None):
     g, sd = _load(golden)
     model = _build(dev)
     assert sorted(model.state_dict().keys()) == sorted(sd.keys())            # checkpoint compatibility (SURVEY §5)
@@ -48,6 +76,11 @@ def _check(golden, dev, tol):
             # LReLu bias gradients are sums of dx over N*H*W with heavy cancellation (|db| << sum|dx|), so the fp32 round-off of
             # a different convolution backend upstream shows up amplified there; db itself is pinned at op level to 1e-5
             lim = 100 * tol if (k.endswith('activation.bias') and dev != 'cpu') else 10 * tol
+            if backend_dev is not None:
+                # measured on B200: with torch ops ONLY the GPU already sits 2.3e-3 (lift bias) / 7.8e-4 (first norm weight) from
+                # the CPU golden on two cancellation-heavy sums (the L1 loss gradient is sign(pred - target): one flipped sign
+                # moves them), identically for the fused and the unfused path; allow what the backend alone produces
+                lim = max(lim, 2 * backend_dev[k])
             assert _rel(named[k[5:]].grad, g[k]) < lim, (k, _rel(named[k[5:]].grad, g[k]))
     # the reference builds decoder_inv[N_layers] but never calls it: same parameters stay without gradient
     assert sorted(k for k, p in named.items() if p.grad is None) == list(g['no_grad_params'])
@@ -61,7 +94,7 @@ def test_mirror_matches_reference_cpu(golden):
 def test_mirror_matches_reference_gpu(golden):
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
-    _check(golden, 'cuda', 5e-5)
+    _check(golden, 'cuda', 5e-5, backend_dev=_torch_backend_deviation(golden, 'cuda'))
 
 
 @pytest.mark.skipif(not os.path.isdir('/root/reference/CNO_Experiments'), reason='reference checkout not present')
