@@ -4,7 +4,9 @@
 // separable filter runs horizontal-then-vertical inside the same CTA (one HBM read + one write; the
 // reference launches two kernels with a round trip through HBM, upfirdn2d.py:235-237), a 2-D filter
 // runs as a direct polyphase gather.  Only taps that meet a real sample are visited.
+#include <stdlib.h>
 #include "common.cuh"
+#include "upfirdn2d_fast.cuh"
 
 namespace {
 
@@ -111,6 +113,21 @@ extern "C" int cno_upfirdn2d(const void* x, void* y, const float* f, int dtype, 
     CNO_CHECK_ARG(fw >= 1 && fh >= 1 && fw <= 64 && fh <= 64, "upfirdn2d: filter size %dx%d not in 1..64", fw, fh);
     CNO_CHECK_ARG(in_h >= 1 && in_w >= 1, "upfirdn2d: empty input plane");
     if (planes <= 0 || out_h <= 0 || out_w <= 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (separable && upx == upy && downx == downy && fw == fh && !getenv("CNO_UPFIRDN_GENERIC")) {
+        // fast path: compile-time polyphase arithmetic, register windows (upfirdn2d_fast.cuh)
+        upfast::Params q{};
+        q.x = x; q.y = y; q.f = f; q.in_h = in_h; q.in_w = in_w; q.out_h = out_h; q.out_w = out_w;
+        q.padx0 = padx0; q.pady0 = pady0; q.flip = flip; q.gain = gain;
+        int rc = -1;
+        switch (dtype) {
+            case CNO_F32: rc = upfast::launch_cfg<float>(q, planes, upx, downx, fw, st); break;
+            case CNO_BF16: rc = upfast::launch_cfg<__nv_bfloat16>(q, planes, upx, downx, fw, st); break;
+            case CNO_F16: rc = upfast::launch_cfg<__half>(q, planes, upx, downx, fw, st); break;
+            default: cno_set_error("upfirdn2d: unsupported dtype %d", dtype); return (int)cudaErrorInvalidValue;
+        }
+        if (rc >= 0) return rc;
+    }
     UpParams p{};
     p.x = x; p.y = y; p.f = f; p.planes = planes; p.in_h = in_h; p.in_w = in_w; p.out_h = out_h; p.out_w = out_w;
     p.fw = fw; p.fh = fh; p.upx = upx; p.upy = upy; p.downx = downx; p.downy = downy; p.padx0 = padx0; p.pady0 = pady0;
@@ -132,7 +149,6 @@ extern "C" int cno_upfirdn2d(const void* x, void* y, const float* f, int dtype, 
     p.tiles_y = (out_h + p.toh - 1) / p.toh;
     const int64_t blocks = planes * p.tiles_x * p.tiles_y;
     CNO_CHECK_ARG(blocks < (1ll << 31), "upfirdn2d: grid too large");
-    cudaStream_t st = (cudaStream_t)stream;
     cudaError_t e = cudaSuccess;
 #define UP_LAUNCH(T) do { \
         if (smem > 48 * 1024) e = cudaFuncSetAttribute(upfirdn2d_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \

@@ -239,6 +239,33 @@ def test_upfirdn2d_full_size_adjoint(cno, shape, f_taps, kw):
     assert rel(y[:1, :2], ref) < 1e-5
 
 
+@pytest.mark.parametrize('up,down,taps', [(1, 1, 4), (1, 1, 12), (2, 1, 4), (2, 1, 8), (2, 1, 12), (2, 1, 16), (2, 1, 24), (4, 1, 4),
+                                          (4, 1, 24), (4, 1, 16), (1, 2, 4), (1, 2, 12), (1, 2, 24), (1, 4, 8), (1, 4, 24)])
+@pytest.mark.parametrize('shape,pad', [((2, 3, 37, 53), [3, 2, 5, 1]), ((1, 2, 150, 141), [-1, 7, 0, -2]), ((3, 2, 8, 8), [6, 5, 6, 5])])
+def test_upfirdn2d_fast_path(cno, up, down, taps, shape, pad):
+    """register-window kernel (csrc/upfirdn2d_fast.cuh): asymmetric random taps (flip conventions matter), odd plane sizes that
+    leave partial tiles and strips, positive and negative padding; vs the oracle and vs the generic kernel."""
+    import os
+    g = torch.Generator().manual_seed(up * 100 + down * 10 + taps)
+    x = torch.randn(*shape, generator=g)
+    f = torch.randn(taps, generator=g)
+    for flip in (False, True):
+        kw = dict(up=up, down=down, padding=pad, flip_filter=flip, gain=1.7)
+        if (shape[3] * up + pad[0] + pad[1] - taps + down) // down < 1 or (shape[2] * up + pad[2] + pad[3] - taps + down) // down < 1:
+            continue
+        y_ref = O.upfirdn2d(x, f, **kw)
+        y = cno.upfirdn2d.upfirdn2d(x.to(DEV), f.to(DEV), **kw)
+        os.environ['CNO_UPFIRDN_GENERIC'] = '1'
+        try:
+            y_gen = cno.upfirdn2d.upfirdn2d(x.to(DEV), f.to(DEV), **kw)
+        finally:
+            del os.environ['CNO_UPFIRDN_GENERIC']
+        assert y.shape == y_ref.shape
+        assert rel(y, y_ref) < 1e-5 and rel(y_gen, y_ref) < 1e-5
+        yb = cno.upfirdn2d.upfirdn2d(x.to(DEV, torch.bfloat16), f.to(DEV), **kw)
+        assert rel(yb, O.upfirdn2d(x.bfloat16().float(), f, **kw)) < 2e-2
+
+
 # ------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize('act', list(O.ACTIVATIONS))
 def test_bias_act_golden(cno, golden, act):
