@@ -4,15 +4,20 @@
 // produce (reference upfirdn2d.py:269-379, filtered_lrelu.py:215-221); everything else runs the generic
 // kernel in upfirdn2d.cu.
 //
-// One CTA = one output tile of one plane, two passes through shared memory (one HBM read, one write):
-//   stage : input footprint -> s_in (fp32, zero filled outside the plane = the padding)
+// One CTA = one output tile of one plane, two passes through shared memory (one HBM read, one write).
+// The whole tile geometry is compile time (tile size, footprint, row pitches), so the passes carry
+// no index arithmetic beyond one constant division per task:
+//   stage : input footprint -> s_in (fp32, zero filled outside the plane = the padding); a warp reads 32
+//           consecutive columns of a row, two rows (2*K loads) in flight per thread
 //   h-pass: a thread owns ONE footprint row and a strip of R consecutive outputs; the WIN input samples of
-//           the strip sit in registers, all polyphase index arithmetic is resolved at compile time because
-//           strips start on a whole input sample ((o*DOWN - pad0) % UP == 0); taps live in registers
+//           the strip are read with 16-byte LDS into registers, polyphase indices are compile time because
+//           the tile grid is shifted so that every strip starts on a whole input sample
+//           ((o*DOWN - pad0) % UP == 0); taps live in registers
 //   v-pass: a thread owns ONE column and a strip of R output rows (register window down the column), and
 //           stores straight to y: a warp writes 32 consecutive elements of a row
-// Row pitches are odd, so "consecutive threads = consecutive rows" (h-pass) and "consecutive threads =
-// consecutive columns" (v-pass) are both bank-conflict free.
+// Row pitches are 4 * odd: consecutive threads = consecutive rows makes the 16-byte accesses of the h-pass
+// conflict free (8 threads of a quarter warp hit 8 different 16-byte bank groups), consecutive threads =
+// consecutive columns makes the scalar accesses of the v-pass conflict free.
 #pragma once
 #include "common.cuh"
 
@@ -22,22 +27,23 @@ struct Params {
     const void* x; void* y; const float* f;      // f: NT horizontal taps then NT vertical taps (device memory)
     int in_h, in_w, out_h, out_w, padx0, pady0, flip;
     float gain;
-    int tow, toh, tiles_x, tiles_y;
-    int pin, ph;                                 // odd row pitches of s_in / s_h
-    int ith;                                     // rows of the (maximal) input footprint
+    int tiles_x, tiles_y;
+    int offx, offy;                              // tile grid shift: tile (tx, ty) starts at output (tx*TOW - offx, ty*TOH - offy)
 };
 
 __host__ __device__ constexpr int strip_len(int up) { return up == 1 ? 4 : (up == 2 ? 8 : 16); }
+__host__ __device__ constexpr int pitch_for(int n) { int p = (n + 3) / 4; return 4 * (p | 1); }   // >= n, multiple of 4, p/4 odd
 
 template <int UP, int DOWN, int NT>
 struct Fir {
     static constexpr int R = strip_len(UP);                               // outputs per strip
     static constexpr int WIN = ((R - 1) * DOWN + NT - 1) / UP + 1;        // input samples a strip touches
+    static constexpr int WIN4 = (WIN + 3) / 4;                            // ... in 16-byte loads
     static constexpr int STEP = R * DOWN / UP;                            // input samples between strips
-    static_assert((R * DOWN) % UP == 0, "strips must start on a whole input sample");
+    static_assert((R * DOWN) % UP == 0 && STEP % 4 == 0, "strips must start on a whole, 16-byte aligned input sample");
     static_assert(NT % UP == 0, "every phase must have the same tap count");
     // out[j] = sum_k g[t0 + k*UP] * w[s0 + k],  t0 = first tap that meets a real sample
-    static __device__ __forceinline__ void run(const float (&w)[WIN], const float (&g)[NT], float (&out)[R]) {
+    static __device__ __forceinline__ void run(const float (&w)[4 * WIN4], const float (&g)[NT], float (&out)[R]) {
 #pragma unroll
         for (int j = 0; j < R; j++) {
             const int t0 = (UP - (j * DOWN) % UP) % UP;
@@ -50,132 +56,154 @@ struct Fir {
     }
 };
 
-__device__ __forceinline__ int floor_div(int a, int b) { int q = a / b; return (a % b != 0 && ((a < 0) != (b < 0))) ? q - 1 : q; }
-__device__ __forceinline__ int pos_mod(int a, int b) { int r = a % b; return r < 0 ? r + b : r; }
-
-template <class T, int UP, int DOWN, int NT>
-__global__ void __launch_bounds__(256) upfirdn2d_fast_kernel(const Params p) {
+// compile-time tile geometry.  SMALL = planes of at most ~64 outputs across
+template <int UP, int DOWN, int NT, bool SMALL>
+struct Geo {
     using F = Fir<UP, DOWN, NT>;
-    constexpr int R = F::R, WIN = F::WIN, STEP = F::STEP;
-    extern __shared__ float smem[];
-    __shared__ float s_f[2 * NT];
-    float* s_in = smem;
-    float* s_h = smem + p.ith * p.pin;
-    const int tid = threadIdx.x, nthr = blockDim.x;
+    static constexpr int TOW = SMALL ? (DOWN == 1 ? 32 : 16) : (DOWN == 1 ? 128 : DOWN == 2 ? 64 : 32);
+    static constexpr int TOH = SMALL ? (DOWN == 1 ? 32 : 16) : (DOWN == 1 ? 64 : DOWN == 2 ? 32 : 16);
+    static constexpr int NSX = TOW / F::R, NSY = TOH / F::R;
+    static constexpr int ITW = (NSX - 1) * F::STEP + F::WIN, ITH = (NSY - 1) * F::STEP + F::WIN;
+    static constexpr int PIN = pitch_for((NSX - 1) * F::STEP + 4 * F::WIN4);
+    static constexpr int PH = pitch_for(TOW);
+    static constexpr int THREADS = (TOW * NSY >= 256 && ITH * NSX >= 256) ? 256 : 128;
+    static constexpr int SPAR = THREADS / TOW;                            // v-pass strips processed in parallel
+    static constexpr int K = (ITW + 31) / 32;                             // 32-column chunks of a footprint row
+    static constexpr size_t SMEM = sizeof(float) * (size_t)ITH * (PIN + PH);
+    static_assert(TOW % F::R == 0 && TOH % F::R == 0 && THREADS % TOW == 0, "tile / strip / thread shapes");
+};
 
-    int b = blockIdx.x;
-    const int tx = b % p.tiles_x; b /= p.tiles_x;
-    const int ty = b % p.tiles_y; const int plane = b / p.tiles_y;
-    const int ox0 = tx * p.tow, oy0 = ty * p.toh;
-    const int tw = min(p.tow, p.out_w - ox0), th = min(p.toh, p.out_h - oy0);
-    // first strip starts ex (ey) outputs before the tile so that it starts on a whole input sample
-    const int ex = (UP > 1) ? pos_mod(ox0 * DOWN - p.padx0, UP) : 0;
-    const int ey = (UP > 1) ? pos_mod(oy0 * DOWN - p.pady0, UP) : 0;
-    const int obx = ox0 - ex, oby = oy0 - ey;
-    const int ibx = floor_div(obx * DOWN - p.padx0, UP), iby = floor_div(oby * DOWN - p.pady0, UP);
-    const int nsx = (tw + ex + R - 1) / R, nsy = (th + ey + R - 1) / R;
-    const int iw = (nsx - 1) * STEP + WIN, ih = (nsy - 1) * STEP + WIN;
+template <class T, int UP, int DOWN, int NT, bool SMALL>
+__global__ void __launch_bounds__(Geo<UP, DOWN, NT, SMALL>::THREADS)
+upfirdn2d_fast_kernel(const Params p) {
+    using F = Fir<UP, DOWN, NT>;
+    using G = Geo<UP, DOWN, NT, SMALL>;
+    constexpr int R = F::R, WIN4 = F::WIN4, STEP = F::STEP;
+    constexpr int PIN = G::PIN, PH = G::PH, ITH = G::ITH, ITW = G::ITW, NW = G::THREADS / 32;
+    extern __shared__ __align__(16) float smem[];
+    __shared__ float s_f[2 * NT];
+    float* s_in = smem;                 // [ITH][PIN]
+    float* s_h = smem + ITH * PIN;      // [ITH][PH]
+    const int tid = threadIdx.x;
+
+    unsigned b = blockIdx.x;
+    const int tx = b % (unsigned)p.tiles_x; b /= (unsigned)p.tiles_x;
+    const int ty = b % (unsigned)p.tiles_y; const int plane = b / (unsigned)p.tiles_y;
+    const int ox0 = tx * G::TOW - p.offx, oy0 = ty * G::TOH - p.offy;
+    const int ibx = (ox0 * DOWN - p.padx0) / UP, iby = (oy0 * DOWN - p.pady0) / UP;      // exact by construction of offx / offy
 
     // taps in correlation order: g[t] = flip ? f[t] : f[NT-1-t]  (upfirdn2d.py:190-191)
     if (tid < 2 * NT) { const int a = tid < NT ? 0 : NT, t = tid - a; s_f[tid] = p.f[a + (p.flip ? t : NT - 1 - t)]; }
 
-    const T* xp = (const T*)p.x + (size_t)plane * p.in_h * p.in_w;
-    for (int r = tid >> 5; r < ih; r += nthr >> 5) {
-        const int sy = iby + r;
-        const bool rok = sy >= 0 && sy < p.in_h;
-        const T* xr = xp + (size_t)(rok ? sy : 0) * p.in_w;
-        for (int c = tid & 31; c < iw; c += 32) {
-            const int sx = ibx + c;
-            s_in[r * p.pin + c] = (rok && sx >= 0 && sx < p.in_w) ? to_f32(xr[sx]) : 0.f;
+    // ---- stage: footprint -> s_in ------------------------------------------------------------------
+    {
+        const T* xp = (const T*)p.x + (size_t)plane * p.in_h * p.in_w;
+        const int warp = tid >> 5, lane = tid & 31;
+        unsigned cmask = 0;              // bit k: column lane + 32k lies inside the plane
+#pragma unroll
+        for (int k = 0; k < G::K; k++) { const int sx = ibx + lane + 32 * k; if (sx >= 0 && sx < p.in_w) cmask |= 1u << k; }
+        for (int r = warp; r < ITH; r += 2 * NW) {
+            float v[2][G::K];
+#pragma unroll
+            for (int u = 0; u < 2; u++) {
+                const int sy = iby + r + u * NW;
+                const bool rok = sy >= 0 && sy < p.in_h;
+                const T* xr = xp + (size_t)(rok ? sy : 0) * p.in_w + (ibx + lane);
+#pragma unroll
+                for (int k = 0; k < G::K; k++) v[u][k] = (rok && ((cmask >> k) & 1u)) ? to_f32(xr[32 * k]) : 0.f;
+            }
+#pragma unroll
+            for (int u = 0; u < 2; u++) {
+                if (r + u * NW < ITH) {
+#pragma unroll
+                    for (int k = 0; k < G::K; k++)
+                        if (lane + 32 * k < PIN) s_in[(r + u * NW) * PIN + lane + 32 * k] = v[u][k];
+                }
+            }
         }
     }
     __syncthreads();
 
+    // ---- h-pass: s_in -> s_h ----------------------------------------------------------------------
     float g[NT];
 #pragma unroll
     for (int t = 0; t < NT; t++) g[t] = s_f[t];
-    for (int task = tid; task < ih * nsx; task += nthr) {
-        const int strip = task / ih, row = task - strip * ih;
-        const float* src = s_in + row * p.pin + strip * STEP;
-        float w[WIN], out[R];
+    for (int task = tid; task < ITH * G::NSX; task += G::THREADS) {
+        const int strip = task / ITH, row = task - strip * ITH;
+        const float4* src = reinterpret_cast<const float4*>(s_in + row * PIN + strip * STEP);
+        float w[4 * WIN4], out[R];
 #pragma unroll
-        for (int i = 0; i < WIN; i++) w[i] = src[i];
+        for (int i = 0; i < WIN4; i++) { const float4 q = src[i]; w[4 * i] = q.x; w[4 * i + 1] = q.y; w[4 * i + 2] = q.z; w[4 * i + 3] = q.w; }
         F::run(w, g, out);
-        float* dst = s_h + row * p.ph + strip * R;
+        float4* dst = reinterpret_cast<float4*>(s_h + row * PH + strip * R);
 #pragma unroll
-        for (int j = 0; j < R; j++) dst[j] = out[j];
+        for (int j = 0; j < R / 4; j++) dst[j] = make_float4(out[4 * j], out[4 * j + 1], out[4 * j + 2], out[4 * j + 3]);
     }
     __syncthreads();
 
+    // ---- v-pass: s_h -> y -------------------------------------------------------------------------
 #pragma unroll
     for (int t = 0; t < NT; t++) g[t] = s_f[NT + t] * p.gain;
-    T* yp = (T*)p.y + (size_t)plane * p.out_h * p.out_w;
-    const int ncols = nsx * R;
-    for (int task = tid; task < nsy * ncols; task += nthr) {
-        const int strip = task / ncols, col = task - strip * ncols;
-        const float* src = s_h + strip * STEP * p.ph + col;
-        float w[WIN], out[R];
+    const int col = tid % G::TOW, ox = ox0 + col;
+    if (ox < 0 || ox >= p.out_w) return;
+    T* yp = (T*)p.y + (size_t)plane * p.out_h * p.out_w + ox;
+    for (int strip = tid / G::TOW; strip < G::NSY; strip += G::SPAR) {
+        const float* src = s_h + strip * STEP * PH + col;
+        float w[4 * WIN4], out[R];
 #pragma unroll
-        for (int i = 0; i < WIN; i++) w[i] = src[i * p.ph];
+        for (int i = 0; i < F::WIN; i++) w[i] = src[i * PH];
         F::run(w, g, out);
-        const int ox = obx + col;
-        if (ox < ox0 || ox >= ox0 + tw) continue;
-        const int oyb = oby + strip * R;
+        const int oyb = oy0 + strip * R;
+        T* dst = yp + (ptrdiff_t)oyb * p.out_w;
+        if (oyb >= 0 && oyb + R <= p.out_h) {
 #pragma unroll
-        for (int j = 0; j < R; j++) {
-            const int oy = oyb + j;
-            if (oy >= oy0 && oy < oy0 + th) yp[(size_t)oy * p.out_w + ox] = from_f32<T>(out[j]);
+            for (int j = 0; j < R; j++) { *dst = from_f32<T>(out[j]); dst += p.out_w; }
+        } else {
+#pragma unroll
+            for (int j = 0; j < R; j++) { if ((unsigned)(oyb + j) < (unsigned)p.out_h) *dst = from_f32<T>(out[j]); dst += p.out_w; }
         }
     }
 }
 
-// host: tile choice + launch.  Returns -1 when (up, down, taps) has no instantiation.
-template <class T, int UP, int DOWN, int NT>
+// host: launch one instantiation
+template <class T, int UP, int DOWN, int NT, bool SMALL>
 int launch(Params p, int64_t planes, cudaStream_t st) {
-    using F = Fir<UP, DOWN, NT>;
-    constexpr int R = F::R;
-    auto roundup = [](int a, int b) { return (a + b - 1) / b * b; };
-    p.tow = p.out_w < 128 ? roundup(p.out_w, R) : 128;
-    p.toh = p.out_h < 64 ? roundup(p.out_h, R) : 64;
-    if (DOWN > 1) { p.tow = p.tow > 64 ? 64 : p.tow; p.toh = p.toh > 32 ? 32 : p.toh; }
-    size_t smem = 0; int tasks = 0;
-    for (;;) {
-        const int nsx = (p.tow + (UP - 1) + R - 1) / R, nsy = (p.toh + (UP - 1) + R - 1) / R;
-        const int itw = (nsx - 1) * F::STEP + F::WIN;
-        p.ith = (nsy - 1) * F::STEP + F::WIN;
-        p.pin = itw | 1; p.ph = (nsx * R) | 1;
-        smem = sizeof(float) * (size_t)p.ith * (p.pin + p.ph);
-        tasks = nsy * nsx * R;
-        if (smem <= 72 * 1024 || p.toh <= R) break;
-        p.toh = roundup(p.toh / 2, R);
-    }
-    if (smem > 200 * 1024) return -1;
-    p.tiles_x = (p.out_w + p.tow - 1) / p.tow;
-    p.tiles_y = (p.out_h + p.toh - 1) / p.toh;
+    using G = Geo<UP, DOWN, NT, SMALL>;
+    auto pos_mod = [](int a, int b) { int r = a % b; return r < 0 ? r + b : r; };
+    p.offx = (UP > 1) ? pos_mod(-p.padx0, UP) : 0;
+    p.offy = (UP > 1) ? pos_mod(-p.pady0, UP) : 0;
+    p.tiles_x = (p.out_w + p.offx + G::TOW - 1) / G::TOW;
+    p.tiles_y = (p.out_h + p.offy + G::TOH - 1) / G::TOH;
     const int64_t blocks = planes * p.tiles_x * p.tiles_y;
     if (blocks >= (1ll << 31)) { cno_set_error("upfirdn2d: grid too large"); return (int)cudaErrorInvalidValue; }
-    int threads = (tasks + 31) / 32 * 32;
-    threads = threads < 64 ? 64 : threads > 256 ? 256 : threads;
-    auto kern = upfirdn2d_fast_kernel<T, UP, DOWN, NT>;
-    static size_t configured = 48 * 1024;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    auto kern = upfirdn2d_fast_kernel<T, UP, DOWN, NT, SMALL>;
+    static bool configured = false;
+    if (!configured && G::SMEM > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
         if (e != cudaSuccess) { cno_set_error("upfirdn2d: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e)); return (int)e; }
-        configured = smem;
     }
-    kern<<<(unsigned)blocks, threads, smem, st>>>(p);
+    configured = true;
+    kern<<<(unsigned)blocks, G::THREADS, G::SMEM, st>>>(p);
     CNO_LAUNCH_CHECK();
     return 0;
 }
 
+template <class T, int UP, int DOWN, int NT>
+int launch_size(const Params& p, int64_t planes, cudaStream_t st) {
+    // small tiles when a large tile would be mostly empty
+    const bool small = p.out_w <= Geo<UP, DOWN, NT, false>::TOW / 2 || p.out_h <= Geo<UP, DOWN, NT, false>::TOH / 2;
+    return small ? launch<T, UP, DOWN, NT, true>(p, planes, st) : launch<T, UP, DOWN, NT, false>(p, planes, st);
+}
+
+// Returns -1 when (up, down, taps) has no instantiation.
 template <class T, int UP, int DOWN>
 int launch_taps(const Params& p, int64_t planes, int nt, cudaStream_t st) {
     switch (nt) {
-        case 4: return launch<T, UP, DOWN, 4>(p, planes, st);
-        case 8: return launch<T, UP, DOWN, 8>(p, planes, st);
-        case 12: return launch<T, UP, DOWN, 12>(p, planes, st);
-        case 16: return launch<T, UP, DOWN, 16>(p, planes, st);
-        case 24: return launch<T, UP, DOWN, 24>(p, planes, st);
+        case 4: return launch_size<T, UP, DOWN, 4>(p, planes, st);
+        case 8: return launch_size<T, UP, DOWN, 8>(p, planes, st);
+        case 12: return launch_size<T, UP, DOWN, 12>(p, planes, st);
+        case 16: return launch_size<T, UP, DOWN, 16>(p, planes, st);
+        case 24: return launch_size<T, UP, DOWN, 24>(p, planes, st);
         default: return -1;
     }
 }
