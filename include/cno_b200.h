@@ -54,7 +54,7 @@ int cno_upfirdn2d(const void* x, void* y, const float* f, int dtype, int separab
  * x>>2 bits 2*(x&3); 1 = negative, 2 = clamped.  sign_mode READ uses offsets (sx, sy) and treats
  * positions outside [0,mask_w) x [0,mask_h) as "pass" (filtered_lrelu.cu:680-687).
  * db: optional fp32[C] accumulator (must be zeroed by the caller): receives sum of y over N,H,W
- * (fuses `db = dx.sum([0,2,3])`, filtered_lrelu.py:257-258).  clamp < 0 or +inf = none. */
+ * (fuses `db = dx.sum([0,2,3])`, filtered_lrelu.py:257-258; sign_mode READ only, else -1).  clamp < 0 or +inf = none. */
 int cno_filtered_lrelu(const void* x, void* y, const void* b, uint8_t* mask, float* db,
                        const float* fu, const float* fd, int dtype,
                        int n, int c, int in_h, int in_w, int out_h, int out_w,

@@ -185,6 +185,10 @@ struct Stream {
     uint32_t colmask;       // WRITE: valid-column bits; READ: valid mask-element bits
     int rd_byte, rd_shift;  // READ: first mask byte of this thread, bit shift
     uint8_t* mrow0;         // mask row 0 of this thread's plane (+ group byte for WRITE)
+    // fused db = y.sum([0,2,3]): sum over the outputs of a row = dot(finished v-down row, column weights), the weight of
+    // column c being the sum of the down taps through which c reaches a valid output column
+    f2 dbw[2], dbacc[2];
+    int db_lo, db_hi;       // rows r of the current body with db_lo <= r < db_hi are real output rows of the segment (set by the caller)
 
     template <class LD>
     FLR_DEV void init(const Params& p, const CtaGeom& cg, int tid, LD ld_bias) {
@@ -196,7 +200,18 @@ struct Stream {
         FLR_UNROLL for (int w = 0; w < C::WLY; w++) { win[w][0] = mk2(0.f, 0.f); win[w][1] = mk2(0.f, 0.f); }
         bE[0] = bE[1] = mk2(0.f, 0.f);
         colmask = 0; rd_byte = 0; rd_shift = 0; mrow0 = nullptr;
+        dbw[0] = dbw[1] = dbacc[0] = dbacc[1] = mk2(0.f, 0.f); db_lo = db_hi = 0;
         if (!active) return;
+        if (MODE == SIGN_READ && p.db) {       // db is a backward quantity: only the mask-reading variant carries the code
+            float w[4];
+            FLR_UNROLL for (int m = 0; m < 4; m++) {
+                const int c = 4 * g + m;
+                w[m] = 0.f;
+                for (int t = c % C::DOWN; t < C::TD && t <= c; t += C::DOWN)
+                    if ((c - t) / C::DOWN < p.OW) w[m] += p.fd[t];
+            }
+            dbw[0] = mk2(w[0], w[1]); dbw[1] = mk2(w[2], w[3]);
+        }
         // bias edge profile: A = hup(x) + b * sum_k [column valid] * tap
         const float bias = p.b ? ld_bias(plane % p.C) : 0.f;
         FLR_UNROLL for (int pr = 0; pr < 2; pr++) {
@@ -326,6 +341,7 @@ struct Stream {
                 const int r = jl / C::DOWN;
                 f4 o; o.x = acc[r][0].x; o.y = acc[r][0].y; o.z = acc[r][1].x; o.w = acc[r][1].y;
                 *reinterpret_cast<f4*>(Dbuf + r * p.dp + dofs) = o;
+                if (MODE == SIGN_READ && r >= db_lo && r < db_hi) { dbacc[0] = ffma2(acc[r][0], dbw[0], dbacc[0]); dbacc[1] = ffma2(acc[r][1], dbw[1], dbacc[1]); }
                 acc[r][0] = mk2(0.f, 0.f); acc[r][1] = mk2(0.f, 0.f);
             }
         }

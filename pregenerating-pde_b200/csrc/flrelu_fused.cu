@@ -33,7 +33,7 @@ extern "C" int cno_filtered_lrelu(const void* x, void* y, const void* b, uint8_t
     CNO_CHECK_ARG(gain > 0.f && slope >= 0.f, "filtered_lrelu: gain must be > 0 and slope >= 0");
     if (dtype != CNO_F32 && dtype != CNO_BF16 && dtype != CNO_F16) return -1;
     if (fu_taps > 32 || fd_taps > 32 || fu_taps < 1 || fd_taps < 1) return -1;
-    if (db) return -1;                                   // fused db accumulation: not in this kernel yet
+    if (db && sign_mode != CNO_SIGN_READ) return -1;     // db is accumulated by the mask-reading (backward) variant only
     if (((uintptr_t)x & 15u) || ((uintptr_t)y & 15u)) return -1;
     Plan plan;
     if (make_plan(plan, cno_dtype_size(dtype), n, c, in_h, in_w, out_h, out_w, fu, fu_taps, fd, fd_taps, up, down,
@@ -41,7 +41,7 @@ extern "C" int cno_filtered_lrelu(const void* x, void* y, const void* b, uint8_t
     Params& p = plan.p;
     if (sign_mode == CNO_SIGN_WRITE)
         CNO_CHECK_ARG(mask_h >= p.UH && mask_pitch >= p.G, "filtered_lrelu: mask [%d rows x %d bytes] smaller than [%d x %d]", mask_h, mask_pitch, p.UH, p.G);
-    p.y = y; p.b = b; p.mask = mask; p.db = nullptr;
+    p.y = y; p.b = b; p.mask = mask; p.db = db;
     if (sign_mode == CNO_SIGN_READ) {
         if (((uintptr_t)mask & 3u) || (mask_pitch & 3)) return -1;     // staged with aligned 32-bit copies
         set_mask_window(plan, sx);

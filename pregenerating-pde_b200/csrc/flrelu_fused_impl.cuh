@@ -89,6 +89,12 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     }
     const bool vec_ok = (p.OW & 3) == 0;
     T* const yb = reinterpret_cast<T*>(p.y);
+    // fused `db = dx.sum([0,2,3])` (filtered_lrelu.py:257-258): the streaming threads sum their finished v-down rows against
+    // per-column tap weights (Stream::dbw); partial sums meet in s_db[plane slot] at the end of a segment and leave with one
+    // global atomic per plane and segment
+    __shared__ float s_db[FLR_MAXT];
+    const bool want_db = MODE == SIGN_READ && p.db != nullptr;
+    if (want_db) { for (int i = tid; i < FLR_MAXT; i += blockDim.x) s_db[i] = 0.f; }
     auto store4 = [&](int plane, int o, int ox, const float* out) {
         T* dst = yb + ((size_t)plane * p.OH + o) * p.OW + ox;
         if (vec_ok) store_quad<T>(dst, out);
@@ -134,6 +140,10 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             if (MODE == SIGN_READ && k + 1 < cg.nbodies)                 // next body's mask rows, in flight during this body
                 stage_mask<C>(p, cg, cg.j_b0 + (k + 1) * C::PB, tid, blockDim.x, M + (size_t)((k + 1) & 1) * mbuf, copy4);
             if (sub == 0) mbar_wait(&bars[slot], (uint32_t)(((gs0 + s) / NSTAGE) & 1));
+            if (want_db) {                        // rows of this body that are real output rows (cf. hdown_phase: o = o0 - (ND-1) + k*KO + r)
+                const int lo = (C::ND - 1) - k * C::KO, hi = (cg.o1 - cg.o0) + (C::ND - 1) - k * C::KO;
+                st.db_lo = lo > 0 ? lo : 0; st.db_hi = hi < C::KO ? hi : C::KO;
+            }
             if (st.active)
                 st.body(p, reinterpret_cast<const T*>(xst + (size_t)slot * p.stage_bytes) + ((size_t)st.unit * C::RS + sub * C::PQ) * p.bwx,
                         cg.row0 + s * C::RS + sub * C::PQ, cg.j_b0 + k * C::PB,
@@ -147,6 +157,25 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         }
         mbar_wait(&full[pb], ppar);               // drain: h-down of the segment's last body
         hdown_phase<T, C>(p, cg, tid, blockDim.x, cg.nbodies - 1, D + pb * dbuf, store4);
+        if (want_db) {
+            // segmented warp reduction: lanes of one plane slot are contiguous
+            const int lane = tid & 31;
+            const int u = st.active ? st.unit : -1;
+            float v = (st.dbacc[0].x + st.dbacc[0].y) + (st.dbacc[1].x + st.dbacc[1].y);
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const float ov = __shfl_down_sync(0xffffffffu, v, d);
+                const int ou = __shfl_down_sync(0xffffffffu, u, d);
+                if (lane + d < 32 && ou == u) v += ov;
+            }
+            const int pu = __shfl_up_sync(0xffffffffu, u, 1);
+            if (u >= 0 && (lane == 0 || pu != u)) atomicAdd(&s_db[u], v);
+            __syncthreads();
+            if (tid < p.P) {
+                if (cg.plane0 + tid < p.NC) atomicAdd(p.db + (cg.plane0 + tid) % p.C, s_db[tid]);
+                s_db[tid] = 0.f;
+            }
+        }
         gs0 += cg.nstages_total;
         gr += cg.o1 - cg.o0;
     }

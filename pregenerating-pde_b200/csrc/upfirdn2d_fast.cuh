@@ -79,7 +79,7 @@ upfirdn2d_fast_kernel(const Params p) {
     using F = Fir<UP, DOWN, NT>;
     using G = Geo<UP, DOWN, NT, SMALL>;
     constexpr int R = F::R, WIN4 = F::WIN4, STEP = F::STEP;
-    constexpr int PIN = G::PIN, PH = G::PH, ITH = G::ITH, ITW = G::ITW, NW = G::THREADS / 32;
+    constexpr int PIN = G::PIN, PH = G::PH, ITH = G::ITH, NW = G::THREADS / 32;
     extern __shared__ __align__(16) float smem[];
     __shared__ float s_f[2 * NT];
     float* s_in = smem;                 // [ITH][PIN]

@@ -133,8 +133,12 @@ def _upfirdn2d_call(x, f, separable, upx, upy, downx, downy, padx0, padx1, pady0
 
 class _FilteredLReluPlugin:
     @staticmethod
-    def filtered_lrelu(x, fu, fd, b, si, up, down, px0, px1, py0, py1, sx, sy, gain, slope, clamp, flip_filter, write_signs):
-        """filtered_lrelu.cpp:8-201 -> (y, so, return_code); return_code -1 = use the generic composition."""
+    def filtered_lrelu(x, fu, fd, b, si, up, down, px0, px1, py0, py1, sx, sy, gain, slope, clamp, flip_filter, write_signs,
+                       db=None):
+        """filtered_lrelu.cpp:8-201 -> (y, so, return_code); return_code -1 = use the generic composition.
+        db (extension, optional): zeroed fp32 [C] tensor that receives y.sum([0,2,3]) from the same kernel."""
+        if db is not None and not (db.dtype == torch.float32 and db.is_contiguous() and db.device == x.device and db.numel() == x.shape[1]):
+            raise RuntimeError('db must be a contiguous float32 [C] tensor on the device of x')
         lib = _lib.load()
         if not x.is_cuda:
             raise RuntimeError('x must reside on CUDA device')
@@ -190,7 +194,7 @@ class _FilteredLReluPlugin:
             mode = _lib.SIGN_READ
         tu, td = host_taps(fu), host_taps(fd)
         with torch.cuda.device(x.device):
-            rc = lib.cno_filtered_lrelu(_ptr(x), _ptr(y), _ptr(b), _ptr(s), None,
+            rc = lib.cno_filtered_lrelu(_ptr(x), _ptr(y), _ptr(b), _ptr(s), _ptr(db),
                                         tu.ctypes.data_as(ctypes.c_void_p), td.ctypes.data_as(ctypes.c_void_p), dt,
                                         n, c, xh, xw, yh, yw, fu.shape[0], fd.shape[0], up, down, px0, py0,
                                         s.shape[2] if s is not None else 0, mask_w, s.shape[3] if s is not None else 0,

@@ -88,7 +88,8 @@ class _FilteredLRelu(torch.autograd.Function):
     """forward(x, fu, fd, b, si, sx, sy, cfg); cfg = (up, down, px0, px1, py0, py1, gain, slope, clamp, flip)."""
 
     @staticmethod
-    def forward(ctx, x, fu, fd, b, si, sx, sy, cfg):
+    def _run(x, fu, fd, b, si, sx, sy, cfg, write_signs, want_db=False):
+        """one fused launch (or the generic composition); returns (y, so, fu, fd, db)"""
         up, down, px0, px1, py0, py1, gain, slope, clamp, flip = cfg
         assert isinstance(x, torch.Tensor) and x.ndim == 4
         if fu is None:
@@ -104,23 +105,33 @@ class _FilteredLRelu(torch.autograd.Function):
             si = torch.empty([0])
         if b is None:
             b = torch.zeros([x.shape[1]], dtype=x.dtype, device=x.device)
-        # the sign mask is produced only when a gradient can be asked for (filtered_lrelu.py:198)
-        write_signs = (si.numel() == 0) and (x.requires_grad or b.requires_grad)
         strides = [x.stride(i) for i in range(x.ndim) if x.size(i) > 1]
         if any(a < c for a, c in zip(strides[:-1], strides[1:])):
             warnings.warn('low-performance memory layout detected in filtered_lrelu input', RuntimeWarning)
         # fused kernel (stream-safe: no global filter staging, unlike filtered_lrelu.py:207-208)
         rc = -1
+        db = torch.zeros([x.shape[1]], dtype=torch.float32, device=x.device) if want_db else None
         if x.dtype in (torch.float16, torch.bfloat16, torch.float32):
             y, so, rc = _plugin.filtered_lrelu(x, fu, fd, b, si, up, down, px0, px1, py0, py1, sx, sy, gain, slope,
-                                               clamp, flip, write_signs)
+                                               clamp, flip, write_signs, db=db)
         if rc < 0:
             # generic composition on our own kernels; keeps only the bit-packed mask (filtered_lrelu.py:215-221)
             y = x.add(b.unsqueeze(-1).unsqueeze(-1))
             y = upfirdn2d.upfirdn2d(x=y, f=fu, up=up, padding=[px0, px1, py0, py1], gain=up ** 2, flip_filter=flip)
             so = _plugin.filtered_lrelu_act_(y, si, sx, sy, gain, slope, clamp, write_signs)
             y = upfirdn2d.upfirdn2d(x=y, f=fd, down=down, flip_filter=flip)
-        ctx.save_for_backward(fu, fd, (si if si.numel() else so))
+            if want_db:
+                db = y.sum([0, 2, 3])
+        if want_db:
+            db = db.to(x.dtype)
+        return y, (si if si.numel() else so), fu, fd, db
+
+    @staticmethod
+    def forward(ctx, x, fu, fd, b, si, sx, sy, cfg):
+        # the sign mask is produced only when a gradient can be asked for (filtered_lrelu.py:198)
+        write_signs = (si is None or si.numel() == 0) and (x.requires_grad or (b is not None and b.requires_grad))
+        y, signs, fu, fd, _ = _FilteredLRelu._run(x, fu, fd, b, si, sx, sy, cfg, write_signs)
+        ctx.save_for_backward(fu, fd, signs)
         ctx.x_shape, ctx.y_shape, ctx.s_ofs, ctx.cfg = x.shape, y.shape, (sx, sy), cfg
         return y
 
@@ -139,7 +150,12 @@ class _FilteredLRelu(torch.autograd.Function):
                   (fu.shape[0] - 1) + (fd.shape[0] - 1) - py0, xh * up - yh * down + py0 - (up - 1))
             gg = gain * (up ** 2) / (down ** 2)
             cfg = (down, up) + pp + (gg, slope, float('inf'), not flip)
-            dx = _FilteredLRelu.apply(dy, fd, fu, None, si, sx - (fu.shape[-1] - 1) + px0, sy - (fu.shape[0] - 1) + py0, cfg)
+            bsx, bsy = sx - (fu.shape[-1] - 1) + px0, sy - (fu.shape[0] - 1) + py0
+            if ctx.needs_input_grad[3] and not (torch.is_grad_enabled() and dy.requires_grad):
+                # first-order backward: db comes out of the same kernel (no second pass over dx)
+                dx, _, _, _, db = _FilteredLRelu._run(dy, fd, fu, None, si, bsx, bsy, cfg, False, want_db=True)
+                return dx, None, None, db, None, None, None, None
+            dx = _FilteredLRelu.apply(dy, fd, fu, None, si, bsx, bsy, cfg)
         if ctx.needs_input_grad[3]:
             db = dx.sum([0, 2, 3])
         return dx, None, None, db, None, None, None, None
