@@ -120,6 +120,18 @@ def run_reference_arm(args):
     }))
 
 
+def _finish(world, dev):
+    """Multi-rank exit.  Tearing down an NCCL communicator whose collectives live in captured CUDA graphs can block in the
+    communicator destructor (seen at 8 ranks), so after a last barrier every rank leaves without running destructors."""
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        torch.cuda.synchronize(dev)
+        sys.stdout.flush(); sys.stderr.flush()
+        os._exit(0)
+
+
 def run_ours(args):
     import torch.distributed as dist
     import pregenerating_pde_b200 as cno
@@ -277,9 +289,8 @@ def run_ours(args):
                              'sample': f"oracle port of impl='ref', fp32 [8,64,128,128] (1/4 of the batch), 8 timed passes, {cpu_dt * 1e3:.0f} ms each"},
             'clocks': clocks,
         }
-        print(json.dumps(out))
-    if world > 1:
-        dist.destroy_process_group()
+        print(json.dumps(out), flush=True)
+    _finish(world, dev)
 
 
 def run_cno_train(args):
@@ -335,9 +346,8 @@ def run_cno_train(args):
                        'batch_per_gpu': B, 'cuda_graph': bool(tr.use_graph), 'parallelism': f'dp{world}', 'grad_allreduce': tr.dp_mode, 'final_loss': round(float(loss), 5)},
             'e2e': {'value': round(world * B / (e2e_ms * 1e-3), 2), 'unit': 'samples/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 4,
                     'ms_per_step': round(e2e_ms, 3)},
-            'clocks': clocks}))
-    if world > 1:
-        dist.destroy_process_group()
+            'clocks': clocks}), flush=True)
+    _finish(world, dev)
 
 
 def main():
