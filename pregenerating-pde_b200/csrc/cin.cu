@@ -12,23 +12,73 @@ namespace {
 
 constexpr int CTA = 256;
 
-// sum over the `gs` threads that share a plane.  gs is a power of two, 8 <= gs <= 1024.
-// red: shared scratch of blockDim/32 floats per slot.
-__device__ __forceinline__ float group_sum(float v, int gs, float* red, int slot) {
+// 16-byte vector held as four 32-bit registers; elements are unpacked with bit operations so that the per-thread copy of the
+// plane stays in registers (an array of __nv_bfloat16 elements ends up in local memory: ptxas reported a 440-byte stack frame).
+template <class T> struct Pack;
+template <> struct Pack<float> {
+    static constexpr int V = 4;
+    static __device__ __forceinline__ void get(const uint4& u, float (&f)[4]) {
+        f[0] = __uint_as_float(u.x); f[1] = __uint_as_float(u.y); f[2] = __uint_as_float(u.z); f[3] = __uint_as_float(u.w);
+    }
+    static __device__ __forceinline__ uint4 put(const float (&f)[4]) {
+        return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]));
+    }
+};
+template <> struct Pack<__nv_bfloat16> {
+    static constexpr int V = 8;
+    static __device__ __forceinline__ void get(const uint4& u, float (&f)[8]) {
+        const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) { f[2 * i] = __uint_as_float(w[i] << 16); f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u); }
+    }
+    static __device__ __forceinline__ uint4 put(const float (&f)[8]) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) { __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]); w[i] = *reinterpret_cast<uint32_t*>(&h); }
+        return make_uint4(w[0], w[1], w[2], w[3]);
+    }
+};
+template <> struct Pack<__half> {
+    static constexpr int V = 8;
+    static __device__ __forceinline__ void get(const uint4& u, float (&f)[8]) {
+        const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) { const float2 v = __half22float2(*reinterpret_cast<const __half2*>(&w[i])); f[2 * i] = v.x; f[2 * i + 1] = v.y; }
+    }
+    static __device__ __forceinline__ uint4 put(const float (&f)[8]) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) { __half2 h = __floats2half2_rn(f[2 * i], f[2 * i + 1]); w[i] = *reinterpret_cast<uint32_t*>(&h); }
+        return make_uint4(w[0], w[1], w[2], w[3]);
+    }
+};
+__device__ __forceinline__ uint4 ldg16_stream(const void* p) {
+    uint4 u;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w) : "l"(p));
+    return u;
+}
+
+// sums of (a, b) over the `gs` threads that share a plane.  gs is a power of two, 8 <= gs <= 1024.
+// red: shared scratch, 2 * blockDim/32 floats per slot; every call site uses its own slot, so one barrier per call suffices.
+__device__ __forceinline__ void group_sum2(float& a, float& b, int gs, float* red, int slot) {
     const int lanes = gs < 32 ? gs : 32;
-    for (int o = lanes >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (gs <= 32) return v;
+    for (int o = lanes >> 1; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+    if (gs <= 32) return;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nw_total = blockDim.x >> 5;
     const int wpg = gs >> 5;                 // warps per group
-    float* buf = red + slot * nw_total;
-    __syncthreads();                         // previous use of this slot is finished
-    if (lane == 0) buf[warp] = v;
+    float2* buf = reinterpret_cast<float2*>(red) + slot * nw_total;
+    if (lane == 0) buf[warp] = make_float2(a, b);
     __syncthreads();
     const int w0 = (warp / wpg) * wpg;
-    float s = 0.f;
-    for (int i = 0; i < wpg; i++) s += buf[w0 + i];
-    return s;
+    float sa = 0.f, sb = 0.f;
+    for (int i = 0; i < wpg; i++) { const float2 v = buf[w0 + i]; sa += v.x; sb += v.y; }
+    a = sa; b = sb;
+}
+__device__ __forceinline__ float group_sum(float v, int gs, float* red, int slot) {
+    float z = 0.f;
+    group_sum2(v, z, gs, red, slot);
+    return v;
 }
 
 // FiLM conditioning computed inside the forward kernel (FILM.forward, CNO_timeModule_CIN.py:62-65):
@@ -54,43 +104,47 @@ __device__ __forceinline__ void film_affine(const CinParams& p, bool live, int64
 
 template <class T, int VPT>
 __global__ void __launch_bounds__(1024) cin_fwd_reg_kernel(CinParams p) {
-    constexpr int V = 16 / sizeof(T);
-    __shared__ float red[4 * 32];
+    constexpr int V = Pack<T>::V;
+    __shared__ float red[8 * 32];
     const int gs = p.gs, ppc = blockDim.x / gs;
     const int64_t plane = (int64_t)blockIdx.x * ppc + threadIdx.x / gs;
     const int t = threadIdx.x % gs;
     const bool live = plane < p.planes;
     const int nvec = p.hw / V;
     const T* xp = (const T*)p.x + (live ? plane : 0) * (int64_t)p.hw;
-    Vec16<T> v[VPT];
-    float sum = 0.f;
+    // the whole plane goes into registers; all loads are issued before anything waits on them
+    uint4 v[VPT];
 #pragma unroll
     for (int k = 0; k < VPT; k++) {
         const int i = t + k * gs;
-        if (live && i < nvec) {
-            v[k] = ld16_stream(xp + (int64_t)i * V);
+        v[k] = (live && i < nvec) ? ldg16_stream(xp + (int64_t)i * V) : make_uint4(0u, 0u, 0u, 0u);
+    }
+    // conditioning (independent of x): its weight loads and reduction overlap the x loads in flight
+    float s = 0.f, q = 0.f;
+    if (p.film.t) film_affine(p, live, plane, t, gs, red, s, q);
+    else if (live) { s = p.scale[plane]; q = p.shift[plane]; }
+    float sum = 0.f;
 #pragma unroll
-            for (int e = 0; e < V; e++) sum += to_f32(v[k].v[e]);
-        }
+    for (int k = 0; k < VPT; k++) {        // padding vectors are zero: they add nothing
+        float f[V]; Pack<T>::get(v[k], f);
+#pragma unroll
+        for (int e = 0; e < V; e++) sum += f[e];
     }
     const float inv_hw = 1.f / (float)p.hw;
     const float mu = group_sum(sum, gs, red, 0) * inv_hw;
     float sq = 0.f;
 #pragma unroll
     for (int k = 0; k < VPT; k++) {
-        const int i = t + k * gs;
-        if (live && i < nvec) {
+        if (t + k * gs < nvec) {
+            float f[V]; Pack<T>::get(v[k], f);
 #pragma unroll
-            for (int e = 0; e < V; e++) { float d = to_f32(v[k].v[e]) - mu; sq = fmaf(d, d, sq); }
+            for (int e = 0; e < V; e++) { const float d = f[e] - mu; sq = fmaf(d, d, sq); }
         }
     }
     const float var = group_sum(sq, gs, red, 1) * inv_hw;
     const float r = rsqrtf(var + p.eps);
-    float s, q;
-    if (p.film.t) film_affine(p, live, plane, t, gs, red, s, q);
     if (!live) return;
     const int ch = (int)(plane % p.c);
-    if (!p.film.t) { s = p.scale[plane]; q = p.shift[plane]; }
     const float a = p.gamma[ch] * s * r;
     const float d0 = p.beta[ch] * s + q - mu * a;
     if (t == 0) { p.mean[plane] = mu; p.rstd[plane] = r; }
@@ -99,18 +153,18 @@ __global__ void __launch_bounds__(1024) cin_fwd_reg_kernel(CinParams p) {
     for (int k = 0; k < VPT; k++) {
         const int i = t + k * gs;
         if (i < nvec) {
-            Vec16<T> o;
+            float f[V]; Pack<T>::get(v[k], f);
 #pragma unroll
-            for (int e = 0; e < V; e++) o.v[e] = from_f32<T>(fmaf(to_f32(v[k].v[e]), a, d0));
-            st16(yp + (int64_t)i * V, o);
+            for (int e = 0; e < V; e++) f[e] = fmaf(f[e], a, d0);
+            *reinterpret_cast<uint4*>(yp + (int64_t)i * V) = Pack<T>::put(f);
         }
     }
 }
 
 template <class T, int VPT>
 __global__ void __launch_bounds__(1024) cin_bwd_reg_kernel(CinParams p) {
-    constexpr int V = 16 / sizeof(T);
-    __shared__ float red[4 * 32];
+    constexpr int V = Pack<T>::V;
+    __shared__ float red[8 * 32];
     const int gs = p.gs, ppc = blockDim.x / gs;
     const int64_t plane = (int64_t)blockIdx.x * ppc + threadIdx.x / gs;
     const int t = threadIdx.x % gs;
@@ -118,24 +172,23 @@ __global__ void __launch_bounds__(1024) cin_bwd_reg_kernel(CinParams p) {
     const int nvec = p.hw / V;
     const int64_t base = (live ? plane : 0) * (int64_t)p.hw;
     const T* xp = (const T*)p.x + base; const T* gp = (const T*)p.dy + base;
-    const float mu = live ? p.mean[plane] : 0.f, r = live ? p.rstd[plane] : 0.f;
-    Vec16<T> vx[VPT], vg[VPT];
-    float s1 = 0.f, s2 = 0.f;
+    uint4 vx[VPT], vg[VPT];
 #pragma unroll
     for (int k = 0; k < VPT; k++) {
         const int i = t + k * gs;
-        if (live && i < nvec) {
-            vx[k] = ld16_stream(xp + (int64_t)i * V);
-            vg[k] = ld16_stream(gp + (int64_t)i * V);
-#pragma unroll
-            for (int e = 0; e < V; e++) {
-                const float g = to_f32(vg[k].v[e]);
-                s1 += g; s2 = fmaf(g, (to_f32(vx[k].v[e]) - mu) * r, s2);
-            }
-        }
+        const bool ok = live && i < nvec;
+        vx[k] = ok ? ldg16_stream(xp + (int64_t)i * V) : make_uint4(0u, 0u, 0u, 0u);
+        vg[k] = ok ? ldg16_stream(gp + (int64_t)i * V) : make_uint4(0u, 0u, 0u, 0u);
     }
-    s1 = group_sum(s1, gs, red, 0);
-    s2 = group_sum(s2, gs, red, 1);
+    const float mu = live ? p.mean[plane] : 0.f, r = live ? p.rstd[plane] : 0.f;
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPT; k++) {        // padding vectors have dy = 0: they add nothing
+        float fx[V], fg[V]; Pack<T>::get(vx[k], fx); Pack<T>::get(vg[k], fg);
+#pragma unroll
+        for (int e = 0; e < V; e++) { s1 += fg[e]; s2 = fmaf(fg[e], (fx[e] - mu) * r, s2); }
+    }
+    group_sum2(s1, s2, gs, red, 0);
     if (!live) return;
     const int ch = (int)(plane % p.c);
     if (t == 0) { p.s1[plane] = s1; p.s2[plane] = s2; }
@@ -147,13 +200,10 @@ __global__ void __launch_bounds__(1024) cin_bwd_reg_kernel(CinParams p) {
     for (int k = 0; k < VPT; k++) {
         const int i = t + k * gs;
         if (i < nvec) {
-            Vec16<T> o;
+            float fx[V], fg[V]; Pack<T>::get(vx[k], fx); Pack<T>::get(vg[k], fg);
 #pragma unroll
-            for (int e = 0; e < V; e++) {
-                const float xh = (to_f32(vx[k].v[e]) - mu) * r;
-                o.v[e] = from_f32<T>(a * (to_f32(vg[k].v[e]) - m1 - xh * m2));
-            }
-            st16(dp + (int64_t)i * V, o);
+            for (int e = 0; e < V; e++) fg[e] = a * (fg[e] - m1 - (fx[e] - mu) * r * m2);
+            *reinterpret_cast<uint4*>(dp + (int64_t)i * V) = Pack<T>::put(fg);
         }
     }
 }
@@ -161,7 +211,7 @@ __global__ void __launch_bounds__(1024) cin_bwd_reg_kernel(CinParams p) {
 // streaming path: one CTA per plane, any hw
 template <class T, bool BWD>
 __global__ void __launch_bounds__(CTA) cin_stream_kernel(CinParams p) {
-    __shared__ float red[4 * 32];
+    __shared__ float red[8 * 32];
     const int64_t plane = blockIdx.x;
     const int64_t base = plane * (int64_t)p.hw;
     const T* xp = (const T*)p.x + base;
@@ -186,7 +236,7 @@ __global__ void __launch_bounds__(CTA) cin_stream_kernel(CinParams p) {
         const float mu = p.mean[plane], r = p.rstd[plane];
         float s1 = 0.f, s2 = 0.f;
         for (int i = threadIdx.x; i < p.hw; i += CTA) { float g = to_f32(gp[i]); s1 += g; s2 = fmaf(g, (to_f32(xp[i]) - mu) * r, s2); }
-        s1 = group_sum(s1, CTA, red, 0); s2 = group_sum(s2, CTA, red, 1);
+        group_sum2(s1, s2, CTA, red, 0);
         if (threadIdx.x == 0) { p.s1[plane] = s1; p.s2[plane] = s2; }
         const float a = p.gamma[ch] * p.scale[plane] * r, m1 = s1 * inv_hw, m2 = s2 * inv_hw;
         T* dp = (T*)p.y + base;
@@ -209,8 +259,7 @@ __device__ __forceinline__ void film_affine(const CinParams& p, bool live, int64
             aq = fmaf(rq[j], fmaf(f.w1b[j], tn, f.b1b[j]), aq);
         }
     }
-    as = group_sum(as, gs, red, 2);
-    aq = group_sum(aq, gs, red, 3);
+    group_sum2(as, aq, gs, red, 2);
     s = 0.f; q = 0.f;
     if (live) {
         const int ch = (int)(plane % p.c);
@@ -264,7 +313,8 @@ __global__ void __launch_bounds__(256) film_bwd_finish_kernel(FilmBwd p) {
     for (int ch = threadIdx.x; ch < p.c; ch += blockDim.x) {   // thread per channel, coalesced over channels
         const float g = p.gamma[ch], b = p.beta[ch];
         float P = 0.f, Q = 0.f, Pq = 0.f, Qq = 0.f;
-        for (int n = 0; n < p.n; n++) {
+#pragma unroll 16
+        for (int n = 0; n < p.n; n++) {          // unrolled: 32 independent loads in flight instead of one L2 round trip per sample
             const float a1 = p.s1[(int64_t)n * p.c + ch], a2 = p.s2[(int64_t)n * p.c + ch], tn = p.t[n];
             const float ds = fmaf(g, a2, b * a1);
             P = fmaf(ds, tn, P); Q += ds; Pq = fmaf(a1, tn, Pq); Qq += a1;
@@ -297,7 +347,9 @@ __global__ void __launch_bounds__(256) film_bwd_finish_kernel(FilmBwd p) {
 template <class T, bool BWD>
 int cin_launch(CinParams p, cudaStream_t st) {
     constexpr int V = 16 / sizeof(T);
-    constexpr int VPT = BWD ? 4 : 8;
+    // 16-byte vectors per thread: bounded by the 64 registers a 1024-thread CTA leaves each thread (16-bit types unpack to twice
+    // as many fp32 values per vector, so they hold half as many)
+    constexpr int VPT = (BWD ? 4 : 8) / (sizeof(T) == 2 ? 2 : 1);
     const bool vec_ok = (p.hw % V == 0) && !(((uintptr_t)p.x | (uintptr_t)p.y | (uintptr_t)p.dy) & 15u);
     const int nvec = p.hw / V;
     int gs = 8;
