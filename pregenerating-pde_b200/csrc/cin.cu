@@ -254,7 +254,8 @@ __device__ __forceinline__ void film_affine(const CinParams& p, bool live, int64
         const int n = (int)(plane / p.c), ch = (int)(plane % p.c);
         const float tn = f.t[n];
         const float* rs = f.W2s + (int64_t)ch * f.lat; const float* rq = f.W2b + (int64_t)ch * f.lat;
-        for (int j = t; j < f.lat; j += gs) {
+#pragma unroll 8
+        for (int j = t; j < f.lat; j += gs) {      // unrolled: small groups (gs = 8) run 16 iterations, their loads must overlap
             as = fmaf(rs[j], fmaf(f.w1s[j], tn, f.b1s[j]), as);
             aq = fmaf(rq[j], fmaf(f.w1b[j], tn, f.b1b[j]), aq);
         }
