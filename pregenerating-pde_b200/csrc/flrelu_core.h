@@ -20,9 +20,11 @@
 #if defined(__CUDACC__)
 #define FLR_DEV __device__ __forceinline__
 #define FLR_UNROLL _Pragma("unroll")
+#define FLR_NOUNROLL _Pragma("unroll 1")
 #else
 #define FLR_DEV inline
 #define FLR_UNROLL
+#define FLR_NOUNROLL
 #include <math.h>
 #include <string.h>
 #endif
@@ -55,6 +57,15 @@ FLR_DEV uint32_t funnel_l(uint32_t lo, uint32_t hi, int s) {
     return __funnelshift_l(lo, hi, s);
 #else
     return (hi << s) | (lo >> (32 - s));
+#endif
+}
+
+// (hi:lo) >> s, lower word, 0 <= s < 32  (SHF.R.W on the device)
+FLR_DEV uint32_t funnel_r(uint32_t lo, uint32_t hi, int s) {
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_r(lo, hi, s);
+#else
+    return s ? (lo >> s) | (hi << (32 - s)) : lo;
 #endif
 }
 
@@ -183,7 +194,7 @@ struct Stream {
     int dofs;               // float offset of this thread's float4 inside a D row
     bool active;
     uint32_t colmask;       // WRITE: valid-column bits; READ: valid mask-element bits
-    int rd_byte, rd_shift;  // READ: first mask byte of this thread, bit shift
+    int rd_word, rd_bits;   // READ: 32-bit word of the staged mask row that holds this thread's first code bit, and its bit position
     uint8_t* mrow0;         // mask row 0 of this thread's plane (+ group byte for WRITE)
     // fused db = y.sum([0,2,3]): sum over the outputs of a row = dot(finished v-down row, column weights), the weight of
     // column c being the sum of the down taps through which c reaches a valid output column
@@ -199,7 +210,7 @@ struct Stream {
         FLR_UNROLL for (int r = 0; r < C::ND; r++) { acc[r][0] = mk2(0.f, 0.f); acc[r][1] = mk2(0.f, 0.f); }
         FLR_UNROLL for (int w = 0; w < C::WLY; w++) { win[w][0] = mk2(0.f, 0.f); win[w][1] = mk2(0.f, 0.f); }
         bE[0] = bE[1] = mk2(0.f, 0.f);
-        colmask = 0; rd_byte = 0; rd_shift = 0; mrow0 = nullptr;
+        colmask = 0; rd_word = 0; rd_bits = 0; mrow0 = nullptr;
         dbw[0] = dbw[1] = dbacc[0] = dbacc[1] = mk2(0.f, 0.f); db_lo = db_hi = 0;
         if (!active) return;
         if (MODE == SIGN_READ && p.db) {       // db is a backward quantity: only the mask-reading variant carries the code
@@ -230,7 +241,7 @@ struct Stream {
         } else if (MODE == SIGN_READ) {
             const int e0 = 4 * g + p.sx;
             const int fl = (e0 >= 0) ? e0 / 4 : -((-e0 + 3) / 4);
-            rd_byte = fl; rd_shift = 2 * (e0 - 4 * fl);
+            rd_word = (fl - p.mws) >> 2; rd_bits = 8 * ((fl - p.mws) & 3) + 2 * (e0 - 4 * fl);     // fl >= mws by construction (set_mask_window)
             FLR_UNROLL for (int m = 0; m < 4; m++) { const int e = e0 + m; if (e >= 0 && e < p.mask_w) colmask |= 3u << (2 * m); }
             mrow0 = p.mask + (int64_t)plane * p.mask_h * p.mask_pitch;
         }
@@ -295,8 +306,9 @@ struct Stream {
 
     // READ: sign codes of one up-res row from the staged mask rows (stage_mask); bytes outside the mask are zero there
     FLR_DEV uint32_t read_code(const Params& p, const uint8_t* mrow) const {
-        const uint32_t b0 = mrow[rd_byte - p.mws], b1 = mrow[rd_byte - p.mws + 1];
-        return (((b1 << 8) | b0) >> rd_shift) & 0xffu & colmask;
+        // the eight code bits may straddle two words: one funnel shift over the aligned pair (the staged buffer has slack for w[1])
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(mrow) + rd_word;
+        return funnel_r(w[0], w[1], rd_bits) & colmask;
     }
 
     // One body: PQ input rows -> PB up-res rows -> KO finished rows of the vertical down-FIR.
@@ -366,13 +378,20 @@ struct Stream {
 // ------------------------------------------------------------------------------------------------
 template <class C, class CP>
 FLR_DEV void stage_mask(const Params& p, const CtaGeom& cg, int jb, int tid, int nthreads, uint8_t* Mdst, CP copy4) {
-    const int nwords = p.P * C::PB * p.mnw;
-    for (int w = tid; w < nwords; w += nthreads) {
-        const int t = w / p.mnw, i = w - t * p.mnw, u = t / C::PB, jl = t - u * C::PB;
-        const int my = jb + jl + p.sy, plane = cg.plane0 + u, byte = p.mws + 4 * i;
-        const bool ok = plane < p.NC && my >= 0 && my < p.mask_h && byte >= 0 && byte < p.mask_pitch;
-        const uint8_t* src = ok ? p.mask + ((int64_t)plane * p.mask_h + my) * p.mask_pitch + byte : p.mask;
-        copy4(Mdst + (size_t)t * p.mstride + 4 * i, src, ok);
+    // a thread owns one 32-bit word column (plane slot u, word i) and walks down the PB rows of the body: the plane / column
+    // bounds and the address are set up once, each row then costs a row-bound predicate, one pointer step and the copy
+    for (int task = tid; task < p.P * p.mnw; task += nthreads) {
+        const int u = task / p.mnw, i = task - u * p.mnw;
+        const int plane = cg.plane0 + u, byte = p.mws + 4 * i, my0 = jb + p.sy;
+        const bool cok = plane < p.NC && byte >= 0 && byte < p.mask_pitch;
+        const int64_t off0 = cok ? ((int64_t)plane * p.mask_h + my0) * p.mask_pitch + byte : 0;
+        uint8_t* dst = Mdst + (size_t)u * C::PB * p.mstride + 4 * i;
+        const uint8_t* src = p.mask + off0;
+        FLR_NOUNROLL for (int jl = 0; jl < C::PB; jl++) {     // rolled: the copies are asynchronous, unrolling only costs registers
+            const bool ok = cok && my0 + jl >= 0 && my0 + jl < p.mask_h;
+            copy4(dst, ok ? src : p.mask, ok);
+            dst += p.mstride; src += p.mask_pitch;
+        }
     }
 }
 

@@ -112,7 +112,7 @@ static inline int make_plan(Plan& plan, int elem_size, int n, int c, int in_h, i
     }
     for (;; P--) {
         const size_t stage = ((size_t)P * rs * bwx * elem_size + 127) / 128 * 128;
-        const size_t total = NSTAGE * stage + (size_t)NDBUF * P * 6 * p.dp * 4 + 64 + (size_t)2 * P * (6 * down) * mstride;
+        const size_t total = NSTAGE * stage + (size_t)NDBUF * P * 6 * p.dp * 4 + 64 + (size_t)2 * P * (6 * down) * mstride + 16;   // +16: read_code loads one word past a row
         if (total <= FLR_SMEM_KB * 1024 || P == 1) { p.stage_bytes = (int)stage; plan.smem_bytes = total; break; }
     }
     if (plan.smem_bytes > 227 * 1024) return -1;
