@@ -39,7 +39,9 @@ int cno_bias_act(const void* x, const void* b, const void* xref, const void* yre
 /* replaces _plugin.upfirdn2d(x, f, upx, upy, downx, downy, padx0, padx1, pady0, pady1, flip, gain)
  * (upfirdn2d.cpp:8-90).  f: DEVICE pointer to fp32 taps, [fh, fw] row major; separable = 1 means f
  * holds fw taps for the horizontal pass followed by fh taps for the vertical pass and both passes run
- * in ONE kernel (the reference needs two launches, upfirdn2d.py:235-237).  Output size must be
+ * in ONE kernel (the reference needs two launches, upfirdn2d.py:235-237).  Separable filters with one resampling direction
+ * ((up,down) in {(1,1),(2,1),(4,1),(1,2),(1,4)} on both axes, 4/8/12/16/24 taps) take a register-window kernel with compile-time
+ * polyphase indices (csrc/upfirdn2d_fast.cuh); every other argument set runs the generic kernel.  Output size must be
  * (in*up + pad0 + pad1 - f + down) / down (upfirdn2d.cpp:27-28). */
 int cno_upfirdn2d(const void* x, void* y, const float* f, int dtype, int separable,
                   int64_t planes, int in_h, int in_w, int out_h, int out_w, int fw, int fh,

@@ -146,6 +146,26 @@ def test_filtered_lrelu_double_backward(cno):
     assert rel(got, ref) < 1e-5
 
 
+def test_filtered_lrelu_db_paths(cno):
+    """db comes from the backward kernel itself in a first-order backward (one launch) and from the differentiable dx.sum when
+    a graph is requested (filtered_lrelu.py:257-258); both must agree with the oracle, and d(db)/d(dy) must exist."""
+    cfg = O.lrelu_config(32, 32)
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(3, 5, 32, 32, generator=g); b = torch.randn(5, generator=g); dy = torch.randn(3, 5, 32, 32, generator=g)
+    w = torch.randn(5, generator=g)
+    xr, br, dr = x.clone().requires_grad_(True), b.clone().requires_grad_(True), dy.clone().requires_grad_(True)
+    y_ref = O.filtered_lrelu(xr, cfg['fu'], cfg['fd'], br, up=2, down=2, padding=cfg['padding'])
+    db_ref, = torch.autograd.grad(y_ref, [br], dr, create_graph=True)
+    g_ref, = torch.autograd.grad((db_ref * w).sum(), [dr])
+    F = cno.filtered_lrelu.filtered_lrelu
+    xg, bg, dg = x.to(DEV).requires_grad_(True), b.to(DEV).requires_grad_(True), dy.to(DEV).requires_grad_(True)
+    y = F(xg, cfg['fu'].to(DEV), cfg['fd'].to(DEV), bg, up=2, down=2, padding=cfg['padding'])
+    db1, = torch.autograd.grad(y, [bg], dy.to(DEV), retain_graph=True)                 # fused in the kernel
+    db2, = torch.autograd.grad(y, [bg], dg, create_graph=True)                         # differentiable form
+    g_dy, = torch.autograd.grad((db2 * w.to(DEV)).sum(), [dg])
+    assert rel(db1, db_ref) < 1e-5 and rel(db2, db_ref) < 1e-5 and rel(g_dy, g_ref) < 1e-5
+
+
 def test_filtered_lrelu_no_grad_and_bands(cno, monkeypatch):
     """forward-only call writes no mask; full-size C1-shaped planes exercise the banded grid."""
     cfg = O.lrelu_config(128, 128)

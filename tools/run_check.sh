@@ -5,3 +5,4 @@ python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.jso
 python bench.py --sweep > gpurun_out/sweep.log 2>&1; tail -2 gpurun_out/sweep.log
 cp profiles/sweep_latest.json gpurun_out/ 2>/dev/null
 python bench.py --workload cno_train --steps 10 --warmup 3 > gpurun_out/bench_train.json 2>> gpurun_out/bench.err; cut -c1-400 gpurun_out/bench_train.json
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
