@@ -81,7 +81,7 @@ def sweep_filtered_lrelu(rows, N, C, s_in, s_out, dtype, reps):
     gg = gain * up * up / (down * down)
     fwd = lambda i: plug.filtered_lrelu(xs[i % nrot], fu, fd, b, e, up, down, px0, px1, py0, py1, 0, 0, gain, slope, float('inf'), False, True)
     bwd = lambda i: plug.filtered_lrelu(dys[i % nrot], fd, fu, zb, masks[i % nrot], down, up, pp[0], pp[1], pp[2], pp[3],
-                                        px0 - (tu - 1), py0 - (tu - 1), gg, slope, float('inf'), True, False)
+                                        px0 - (tu - 1), py0 - (tu - 1), gg, slope, float('inf'), True, False, signs_only=True)
     cfgname = 'I' if s_in == s_out else ('D' if s_out < s_in else 'U')
     shape = f'[{N},{C},{s_in}->{s_out}] {cfgname}'
     rows.append(row('filtered_lrelu', shape, dtype, 'fwd', time_graph(fwd, nrot, reps), nbytes))

@@ -21,7 +21,9 @@ extern "C" {
 #endif
 
 enum { CNO_F32 = 0, CNO_BF16 = 1, CNO_F16 = 2, CNO_F64 = 3 };
-enum { CNO_SIGN_NONE = 0, CNO_SIGN_WRITE = 1, CNO_SIGN_READ = 2 };
+/* CNO_SIGN_READ_SIGNONLY (cno_filtered_lrelu only): like READ, for masks the caller knows were written with clamp = none, so
+ * no code has the "clamped" bit; the kernel then skips that test (11 % faster backward).  READ is always correct. */
+enum { CNO_SIGN_NONE = 0, CNO_SIGN_WRITE = 1, CNO_SIGN_READ = 2, CNO_SIGN_READ_SIGNONLY = 3 };
 
 int cno_version(void);
 /* last error text of the calling thread ("" if none) */

@@ -7,7 +7,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get('CNO_B200_LIB') or os.path.join(_HERE, 'libcno_b200.so')
 
 F32, BF16, F16, F64 = 0, 1, 2, 3
-SIGN_NONE, SIGN_WRITE, SIGN_READ = 0, 1, 2
+SIGN_NONE, SIGN_WRITE, SIGN_READ, SIGN_READ_SIGNONLY = 0, 1, 2, 3
 
 _P, _I, _L, _F = C.c_void_p, C.c_int, C.c_int64, C.c_float
 SIGNATURES = {

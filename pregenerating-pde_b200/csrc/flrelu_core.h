@@ -77,7 +77,9 @@ FLR_DEV uint32_t f_bits(float v) {
 #endif
 }
 
-enum { SIGN_NONE = 0, SIGN_WRITE = 1, SIGN_READ = 2 };
+// SIGN_READ_SO: the caller guarantees the mask holds sign codes only (it was written with clamp = none): the "clamped" bit is not tested
+enum { SIGN_NONE = 0, SIGN_WRITE = 1, SIGN_READ = 2, SIGN_READ_SO = 3 };
+#define FLR_IS_READ(MODE) (((MODE) & 2) != 0)
 
 // element -> fp32 (specialised for bf16 / fp16 by flrelu_fused.cu)
 template <class T> struct Cvt;
@@ -213,7 +215,7 @@ struct Stream {
         colmask = 0; rd_word = 0; rd_bits = 0; mrow0 = nullptr;
         dbw[0] = dbw[1] = dbacc[0] = dbacc[1] = mk2(0.f, 0.f); db_lo = db_hi = 0;
         if (!active) return;
-        if (MODE == SIGN_READ && p.db) {       // db is a backward quantity: only the mask-reading variant carries the code
+        if (FLR_IS_READ(MODE) && p.db) {       // db is a backward quantity: only the mask-reading variant carries the code
             float w[4];
             FLR_UNROLL for (int m = 0; m < 4; m++) {
                 const int c = 4 * g + m;
@@ -238,7 +240,7 @@ struct Stream {
         if (MODE == SIGN_WRITE) {
             FLR_UNROLL for (int m = 0; m < 4; m++) if (4 * g + m < p.UW) colmask |= 1u << (2 * m);   // bit 0 of each 2-bit code
             mrow0 = p.mask + (int64_t)plane * p.mask_h * p.mask_pitch + g;
-        } else if (MODE == SIGN_READ) {
+        } else if (FLR_IS_READ(MODE)) {
             const int e0 = 4 * g + p.sx;
             const int fl = (e0 >= 0) ? e0 / 4 : -((-e0 + 3) / 4);
             rd_word = (fl - p.mws) >> 2; rd_bits = 8 * ((fl - p.mws) & 3) + 2 * (e0 - 4 * fl);     // fl >= mws by construction (set_mask_window)
@@ -282,10 +284,12 @@ struct Stream {
     // (clamp is not handled by the fused kernel: the host plan refuses it and the caller composes
     //  the generic path, exactly like an unsupported filter shape.)
     FLR_DEV void act(const Params& p, f2 v[2], uint32_t& code) {
-        if (MODE == SIGN_READ) {
+        if (FLR_IS_READ(MODE)) {
             float m[4];
             FLR_UNROLL for (int i = 0; i < 4; i++) m[i] = (code & (1u << (2 * i))) ? p.slope : 1.f;
-            if (code & 0xaau) {                     // "clamped" codes written by the generic forward path
+            // "clamped" codes exist only in masks written by the generic forward path with clamp != none; the four extra
+            // test / select pairs cost 11 % of the backward launch, so callers that know the mask's origin use SIGN_READ_SO
+            if (MODE == SIGN_READ && (code & 0xaau)) {
                 FLR_UNROLL for (int i = 0; i < 4; i++) if (code & (2u << (2 * i))) m[i] = 0.f;
             }
             const f2 z = mk2(0.f, 0.f);
@@ -328,7 +332,7 @@ struct Stream {
             }
             const int j = jb + jl;
             uint32_t code = 0;
-            if (MODE == SIGN_READ) code = read_code(p, Mrows + jl * p.mstride);
+            if (FLR_IS_READ(MODE)) code = read_code(p, Mrows + jl * p.mstride);
             // vertical polyphase up-FIR (taps carry UP * gain)
             f2 v[2] = {mk2(0.f, 0.f), mk2(0.f, 0.f)};
             FLR_UNROLL for (int k = 0; k < C::NTU; k++) {
@@ -353,7 +357,7 @@ struct Stream {
                 const int r = jl / C::DOWN;
                 f4 o; o.x = acc[r][0].x; o.y = acc[r][0].y; o.z = acc[r][1].x; o.w = acc[r][1].y;
                 *reinterpret_cast<f4*>(Dbuf + r * p.dp + dofs) = o;
-                if (MODE == SIGN_READ && r >= db_lo && r < db_hi) { dbacc[0] = ffma2(acc[r][0], dbw[0], dbacc[0]); dbacc[1] = ffma2(acc[r][1], dbw[1], dbacc[1]); }
+                if (FLR_IS_READ(MODE) && r >= db_lo && r < db_hi) { dbacc[0] = ffma2(acc[r][0], dbw[0], dbacc[0]); dbacc[1] = ffma2(acc[r][1], dbw[1], dbacc[1]); }
                 acc[r][0] = mk2(0.f, 0.f); acc[r][1] = mk2(0.f, 0.f);
             }
         }

@@ -28,12 +28,13 @@ extern "C" int cno_filtered_lrelu(const void* x, void* y, const void* b, uint8_t
                                   int mask_h, int mask_w, int mask_pitch, int sx, int sy, int sign_mode,
                                   float gain, float slope, float clamp, int flip, void* stream) {
     CNO_CHECK_ARG(x && y && fu && fd, "filtered_lrelu: null pointer");
-    CNO_CHECK_ARG(sign_mode >= 0 && sign_mode <= 2, "filtered_lrelu: bad sign_mode %d", sign_mode);
+    CNO_CHECK_ARG(sign_mode >= 0 && sign_mode <= 3, "filtered_lrelu: bad sign_mode %d", sign_mode);
+    const bool reading = sign_mode == CNO_SIGN_READ || sign_mode == CNO_SIGN_READ_SIGNONLY;
     CNO_CHECK_ARG(sign_mode == CNO_SIGN_NONE || mask, "filtered_lrelu: sign_mode %d needs a mask", sign_mode);
     CNO_CHECK_ARG(gain > 0.f && slope >= 0.f, "filtered_lrelu: gain must be > 0 and slope >= 0");
     if (dtype != CNO_F32 && dtype != CNO_BF16 && dtype != CNO_F16) return -1;
     if (fu_taps > 32 || fd_taps > 32 || fu_taps < 1 || fd_taps < 1) return -1;
-    if (db && sign_mode != CNO_SIGN_READ) return -1;     // db is accumulated by the mask-reading (backward) variant only
+    if (db && !reading) return -1;     // db is accumulated by the mask-reading (backward) variant only
     if (((uintptr_t)x & 15u) || ((uintptr_t)y & 15u)) return -1;
     Plan plan;
     if (make_plan(plan, cno_dtype_size(dtype), n, c, in_h, in_w, out_h, out_w, fu, fu_taps, fd, fd_taps, up, down,
@@ -42,7 +43,7 @@ extern "C" int cno_filtered_lrelu(const void* x, void* y, const void* b, uint8_t
     if (sign_mode == CNO_SIGN_WRITE)
         CNO_CHECK_ARG(mask_h >= p.UH && mask_pitch >= p.G, "filtered_lrelu: mask [%d rows x %d bytes] smaller than [%d x %d]", mask_h, mask_pitch, p.UH, p.G);
     p.y = y; p.b = b; p.mask = mask; p.db = db;
-    if (sign_mode == CNO_SIGN_READ) {
+    if (reading) {
         if (((uintptr_t)mask & 3u) || (mask_pitch & 3)) return -1;     // staged with aligned 32-bit copies
         set_mask_window(plan, sx);
     }

@@ -93,7 +93,7 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     // per-column tap weights (Stream::dbw); partial sums meet in s_db[plane slot] at the end of a segment and leave with one
     // global atomic per plane and segment
     __shared__ float s_db[FLR_MAXT];
-    const bool want_db = MODE == SIGN_READ && p.db != nullptr;
+    const bool want_db = FLR_IS_READ(MODE) && p.db != nullptr;
     if (want_db) { for (int i = tid; i < FLR_MAXT; i += blockDim.x) s_db[i] = 0.f; }
     auto store4 = [&](int plane, int o, int ox, const float* out) {
         T* dst = yb + ((size_t)plane * p.OH + o) * p.OW + ox;
@@ -122,10 +122,10 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         Stream<T, C, MODE> st;
         st.init(p, cg, tid, [&](int ch) { return Cvt<T>::get(reinterpret_cast<const T*>(p.b)[ch]); });
 
-        if (MODE == SIGN_READ) stage_mask<C>(p, cg, cg.j_b0, tid, blockDim.x, M, copy4);
+        if (FLR_IS_READ(MODE)) stage_mask<C>(p, cg, cg.j_b0, tid, blockDim.x, M, copy4);
         mbar_wait(&bars[gs0 % NSTAGE], (uint32_t)((gs0 / NSTAGE) & 1));
         if (st.active) st.prologue(p, reinterpret_cast<const T*>(xst + (size_t)(gs0 % NSTAGE) * p.stage_bytes) + (size_t)st.unit * C::RS * p.bwx, cg.row0);
-        if (MODE == SIGN_READ) { asm volatile("cp.async.wait_all;" ::: "memory"); __syncthreads(); }
+        if (FLR_IS_READ(MODE)) { asm volatile("cp.async.wait_all;" ::: "memory"); __syncthreads(); }
 
         int pb = 0; uint32_t ppar = 0;            // slot / parity of the previous body
         for (int k = 0; k < cg.nbodies; k++) {
@@ -137,7 +137,7 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                     while (next_load < cg.nstages_total && next_load < consumed + NSTAGE) issue(next_load++);
                 }
             }
-            if (MODE == SIGN_READ && k + 1 < cg.nbodies)                 // next body's mask rows, in flight during this body
+            if (FLR_IS_READ(MODE) && k + 1 < cg.nbodies)                 // next body's mask rows, in flight during this body
                 stage_mask<C>(p, cg, cg.j_b0 + (k + 1) * C::PB, tid, blockDim.x, M + (size_t)((k + 1) & 1) * mbuf, copy4);
             if (sub == 0) mbar_wait(&bars[slot], (uint32_t)(((gs0 + s) / NSTAGE) & 1));
             if (want_db) {                        // rows of this body that are real output rows (cf. hdown_phase: o = o0 - (ND-1) + k*KO + r)
@@ -149,7 +149,7 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                         cg.row0 + s * C::RS + sub * C::PQ, cg.j_b0 + k * C::PB,
                         D + db * dbuf + (size_t)st.unit * C::KO * p.dp,
                         M + (size_t)(k & 1) * mbuf + (size_t)st.unit * C::PB * p.mstride);
-            if (MODE == SIGN_READ) asm volatile("cp.async.wait_all;" ::: "memory");
+            if (FLR_IS_READ(MODE)) asm volatile("cp.async.wait_all;" ::: "memory");
             mbar_arrive(&full[db]);
             if (k > 0) hdown_phase<T, C>(p, cg, tid, blockDim.x, k - 1, D + pb * dbuf, store4);
             pb = db; ppar = dpar;
@@ -230,6 +230,7 @@ template <class T, class C>
 int launch_mode(const Plan& plan, const CUtensorMap& map, int mode, cudaStream_t st) {
     if (mode == CNO_SIGN_WRITE) return launch_variant<T, C, SIGN_WRITE>(plan, map, st);
     if (mode == CNO_SIGN_READ) return launch_variant<T, C, SIGN_READ>(plan, map, st);
+    if (mode == CNO_SIGN_READ_SIGNONLY) return launch_variant<T, C, SIGN_READ_SO>(plan, map, st);
     return launch_variant<T, C, SIGN_NONE>(plan, map, st);
 }
 

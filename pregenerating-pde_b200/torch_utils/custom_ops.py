@@ -134,9 +134,11 @@ def _upfirdn2d_call(x, f, separable, upx, upy, downx, downy, padx0, padx1, pady0
 class _FilteredLReluPlugin:
     @staticmethod
     def filtered_lrelu(x, fu, fd, b, si, up, down, px0, px1, py0, py1, sx, sy, gain, slope, clamp, flip_filter, write_signs,
-                       db=None):
+                       db=None, signs_only=False):
         """filtered_lrelu.cpp:8-201 -> (y, so, return_code); return_code -1 = use the generic composition.
-        db (extension, optional): zeroed fp32 [C] tensor that receives y.sum([0,2,3]) from the same kernel."""
+        db (extension, optional): zeroed fp32 [C] tensor that receives y.sum([0,2,3]) from the same kernel.
+        signs_only (extension, optional): the caller knows `si` was written with clamp = none (no "clamped" codes), which lets
+        the kernel skip that test; the default is always correct."""
         if db is not None and not (db.dtype == torch.float32 and db.is_contiguous() and db.device == x.device and db.numel() == x.shape[1]):
             raise RuntimeError('db must be a contiguous float32 [C] tensor on the device of x')
         lib = _lib.load()
@@ -191,7 +193,7 @@ class _FilteredLReluPlugin:
                     and s.shape[0] == n and s.shape[1] == c):
                 raise RuntimeError('signs must be a contiguous uint8 [N,C,sh,sw/4] tensor on the device of x')
             mask_w = s.shape[3] << 2
-            mode = _lib.SIGN_READ
+            mode = _lib.SIGN_READ_SIGNONLY if signs_only else _lib.SIGN_READ
         tu, td = host_taps(fu), host_taps(fd)
         with torch.cuda.device(x.device):
             rc = lib.cno_filtered_lrelu(_ptr(x), _ptr(y), _ptr(b), _ptr(s), _ptr(db),

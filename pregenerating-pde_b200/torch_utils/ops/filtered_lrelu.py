@@ -57,7 +57,7 @@ def filtered_lrelu(x, fu=None, fd=None, b=None, up=1, down=1, padding=0, gain=np
         _check_scalars(up, down, gain, slope, clamp)
         cfg = (up, down) + _parse_padding(padding) + (float(gain), float(slope),
                                                        float('inf') if clamp is None else float(clamp), bool(flip_filter))
-        return _FilteredLRelu.apply(x, fu, fd, b, None, 0, 0, cfg)
+        return _FilteredLRelu.apply(x, fu, fd, b, None, 0, 0, cfg, False)
     return _filtered_lrelu_ref(x, fu=fu, fd=fd, b=b, up=up, down=down, padding=padding, gain=gain, slope=slope,
                                clamp=clamp, flip_filter=flip_filter)
 
@@ -85,10 +85,11 @@ def _filtered_lrelu_ref(x, fu=None, fd=None, b=None, up=1, down=1, padding=0, ga
 
 
 class _FilteredLRelu(torch.autograd.Function):
-    """forward(x, fu, fd, b, si, sx, sy, cfg); cfg = (up, down, px0, px1, py0, py1, gain, slope, clamp, flip)."""
+    """forward(x, fu, fd, b, si, sx, sy, cfg, signs_only); cfg = (up, down, px0, px1, py0, py1, gain, slope, clamp, flip);
+    signs_only: the given mask `si` is known to hold sign codes only (written with clamp = none)."""
 
     @staticmethod
-    def _run(x, fu, fd, b, si, sx, sy, cfg, write_signs, want_db=False):
+    def _run(x, fu, fd, b, si, sx, sy, cfg, write_signs, want_db=False, signs_only=False):
         """one fused launch (or the generic composition); returns (y, so, fu, fd, db)"""
         up, down, px0, px1, py0, py1, gain, slope, clamp, flip = cfg
         assert isinstance(x, torch.Tensor) and x.ndim == 4
@@ -113,7 +114,7 @@ class _FilteredLRelu(torch.autograd.Function):
         db = torch.zeros([x.shape[1]], dtype=torch.float32, device=x.device) if want_db else None
         if x.dtype in (torch.float16, torch.bfloat16, torch.float32):
             y, so, rc = _plugin.filtered_lrelu(x, fu, fd, b, si, up, down, px0, px1, py0, py1, sx, sy, gain, slope,
-                                               clamp, flip, write_signs, db=db)
+                                               clamp, flip, write_signs, db=db, signs_only=signs_only)
         if rc < 0:
             # generic composition on our own kernels; keeps only the bit-packed mask (filtered_lrelu.py:215-221)
             y = x.add(b.unsqueeze(-1).unsqueeze(-1))
@@ -127,12 +128,15 @@ class _FilteredLRelu(torch.autograd.Function):
         return y, (si if si.numel() else so), fu, fd, db
 
     @staticmethod
-    def forward(ctx, x, fu, fd, b, si, sx, sy, cfg):
+    def forward(ctx, x, fu, fd, b, si, sx, sy, cfg, signs_only):
         # the sign mask is produced only when a gradient can be asked for (filtered_lrelu.py:198)
-        write_signs = (si is None or si.numel() == 0) and (x.requires_grad or (b is not None and b.requires_grad))
-        y, signs, fu, fd, _ = _FilteredLRelu._run(x, fu, fd, b, si, sx, sy, cfg, write_signs)
+        given = si is not None and si.numel() > 0
+        write_signs = (not given) and (x.requires_grad or (b is not None and b.requires_grad))
+        y, signs, fu, fd, _ = _FilteredLRelu._run(x, fu, fd, b, si, sx, sy, cfg, write_signs, signs_only=given and signs_only)
         ctx.save_for_backward(fu, fd, signs)
         ctx.x_shape, ctx.y_shape, ctx.s_ofs, ctx.cfg = x.shape, y.shape, (sx, sy), cfg
+        # a mask written here holds "clamped" codes only if this call clamps; a given mask keeps what its writer said
+        ctx.signs_only = bool(signs_only) if given else (cfg[8] == float('inf'))
         return y
 
     @staticmethod
@@ -153,9 +157,9 @@ class _FilteredLRelu(torch.autograd.Function):
             bsx, bsy = sx - (fu.shape[-1] - 1) + px0, sy - (fu.shape[0] - 1) + py0
             if ctx.needs_input_grad[3] and not (torch.is_grad_enabled() and dy.requires_grad):
                 # first-order backward: db comes out of the same kernel (no second pass over dx)
-                dx, _, _, _, db = _FilteredLRelu._run(dy, fd, fu, None, si, bsx, bsy, cfg, False, want_db=True)
-                return dx, None, None, db, None, None, None, None
-            dx = _FilteredLRelu.apply(dy, fd, fu, None, si, bsx, bsy, cfg)
+                dx, _, _, _, db = _FilteredLRelu._run(dy, fd, fu, None, si, bsx, bsy, cfg, False, want_db=True, signs_only=ctx.signs_only)
+                return dx, None, None, db, None, None, None, None, None
+            dx = _FilteredLRelu.apply(dy, fd, fu, None, si, bsx, bsy, cfg, ctx.signs_only)
         if ctx.needs_input_grad[3]:
             db = dx.sum([0, 2, 3])
-        return dx, None, None, db, None, None, None, None
+        return dx, None, None, db, None, None, None, None, None

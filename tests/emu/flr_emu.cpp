@@ -38,14 +38,14 @@ static void run(const Plan& plan, const float* x, float* y, const float* bias) {
             int next_load = 0;
             auto issue = [&](int s) { tma((gs0 + s) % NSTAGE, cg.row0 + s * C::RS, cg.plane0); };
             while (next_load < cg.nstages_total && next_load < NSTAGE) issue(next_load++);
-            if (MODE == SIGN_READ) for (int t = 0; t < nthreads; t++) stage_mask<C>(p, cg, cg.j_b0, t, nthreads, M.data(), copy4);
+            if (FLR_IS_READ(MODE)) for (int t = 0; t < nthreads; t++) stage_mask<C>(p, cg, cg.j_b0, t, nthreads, M.data(), copy4);
             for (int t = 0; t < nthreads; t++) {
                 th[t].init(p, cg, t, [&](int ch) { return bias[ch]; });
                 if (th[t].active) th[t].prologue(p, xst.data() + ((size_t)(gs0 % NSTAGE) * p.P + th[t].unit) * C::RS * p.bwx, cg.row0);
             }
             for (int k = 0; k < cg.nbodies; k++) {
                 const int s = 1 + k / C::M, slot = (gs0 + s) % NSTAGE;
-                if (MODE == SIGN_READ && k + 1 < cg.nbodies) for (int t = 0; t < nthreads; t++)
+                if (FLR_IS_READ(MODE) && k + 1 < cg.nbodies) for (int t = 0; t < nthreads; t++)
                     stage_mask<C>(p, cg, cg.j_b0 + (k + 1) * C::PB, t, nthreads, M.data() + (size_t)((k + 1) & 1) * mbuf, copy4);
                 for (int t = 0; t < nthreads; t++) if (th[t].active)
                     th[t].body(p, xst.data() + (size_t)slot * p.P * C::RS * p.bwx + ((size_t)th[t].unit * C::RS + (k % C::M) * C::PQ) * p.bwx,
@@ -67,6 +67,7 @@ template <class C>
 static void run_mode(const Plan& plan, int mode, const float* x, float* y, const float* b) {
     if (mode == SIGN_WRITE) run<C, SIGN_WRITE>(plan, x, y, b);
     else if (mode == SIGN_READ) run<C, SIGN_READ>(plan, x, y, b);
+    else if (mode == SIGN_READ_SO) run<C, SIGN_READ_SO>(plan, x, y, b);
     else run<C, SIGN_NONE>(plan, x, y, b);
 }
 
@@ -79,7 +80,7 @@ extern "C" int flr_emulate(const float* x, float* y, const float* b, uint8_t* ma
                   clamp, flip, ctas) != 0) return -1;
     plan.p.b = b; plan.p.mask = mask; plan.p.mask_h = mask_h; plan.p.mask_w = mask_w; plan.p.mask_pitch = mask_pitch;
     plan.p.sx = sx; plan.p.sy = sy;
-    if (mode == SIGN_READ) set_mask_window(plan, sx);
+    if (mode == SIGN_READ || mode == SIGN_READ_SO) set_mask_window(plan, sx);
     if (info) { info[0] = plan.p.P; info[1] = plan.threads; info[2] = plan.blocks; info[3] = plan.p.ncta; info[4] = (int)plan.smem_bytes; }
 #define V(U, D, R) if (plan.up == U && plan.down == D && plan.rx == R && plan.ry == R) { run_mode<Cfg<U, D, R, R>>(plan, mode, x, y, b); return 0; }
     V(2, 2, 0) V(2, 2, 1) V(2, 4, 0) V(2, 4, 1) V(4, 2, 0) V(4, 2, 1) V(4, 2, 2) V(4, 2, 3)

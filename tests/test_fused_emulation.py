@@ -96,6 +96,10 @@ def test_emulated_forward_backward(name, s_in, s_out, N, C, bands):
     assert dx.shape == tuple(x.shape)
     assert rel(dx, dx_ref.numpy()) < 2e-6
     assert rel(dx.sum((0, 2, 3)), db_ref.numpy()) < 1e-5
+    # sign-only read mode (mask known to be written with clamp = none): identical result
+    rc, dx_so, _, _ = run_emu(dy.numpy(), None, fd.numpy(), fu.numpy(), down, up, pp, gg, slope, None, True, 3,
+                              mask=mask, mask_geom=(sh, swv, swb), sxy=(sx, sy), bands=bands)
+    assert rc == 0 and np.array_equal(dx_so, dx)
 
 
 def test_emulated_flip_asymmetric_none_mode():

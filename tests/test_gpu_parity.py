@@ -146,6 +146,34 @@ def test_filtered_lrelu_double_backward(cno):
     assert rel(got, ref) < 1e-5
 
 
+def test_filtered_lrelu_clamped_mask_read_by_fused_backward(cno):
+    """CNO filters with clamp: the forward takes the generic composition (the fused kernel refuses clamp) and writes "clamped"
+    codes; the backward is a fused launch in READ mode, which must honour them.  A mask written by the fused forward (clamp =
+    none) gives the same dx in READ and READ_SIGNONLY mode."""
+    cfg = O.lrelu_config(32, 32)
+    g = torch.Generator().manual_seed(21)
+    x = torch.randn(2, 4, 32, 32, generator=g); b = torch.randn(4, generator=g); dy = torch.randn(2, 4, 32, 32, generator=g)
+    xr, br = x.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    y_ref = O.filtered_lrelu(xr, cfg['fu'], cfg['fd'], br, up=2, down=2, padding=cfg['padding'], clamp=0.5)
+    dx_ref, db_ref = torch.autograd.grad(y_ref, [xr, br], dy)
+    assert float((y_ref.abs() > 0).float().mean()) > 0.5
+    y, dx, db, mask = fl_case(cno, x, b, dy, cfg, clamp=0.5)
+    assert int((mask & 0xAA).count_nonzero()) > 0                    # clamped codes are present
+    assert rel(y, y_ref) < 1e-5 and rel(dx, dx_ref) < 1e-5 and rel(db, db_ref) < 1e-5
+    # direct plugin calls on a sign-only mask
+    plug = cno.custom_ops.get_plugin('filtered_lrelu_plugin')
+    fu, fd = cfg['fu'].to(DEV), cfg['fd'].to(DEV)
+    px0, px1, py0, py1 = cfg['padding']
+    e = torch.empty(0)
+    y2, so, rc = plug.filtered_lrelu(x.to(DEV), fu, fd, b.to(DEV), e, 2, 2, px0, px1, py0, py1, 0, 0, math.sqrt(2), 0.2, float('inf'), False, True)
+    assert rc == 0 and int((so & 0xAA).count_nonzero()) == 0
+    pp = (22 - px0, px0 - 1, 22 - py0, py0 - 1)
+    zb = torch.zeros(4, device=DEV)
+    outs = [plug.filtered_lrelu(dy.to(DEV), fd, fu, zb, so, 2, 2, pp[0], pp[1], pp[2], pp[3], px0 - 11, py0 - 11, math.sqrt(2), 0.2,
+                                float('inf'), True, False, signs_only=flag) for flag in (False, True)]
+    assert outs[0][2] == 0 and outs[1][2] == 0 and torch.equal(outs[0][0], outs[1][0])
+
+
 def test_filtered_lrelu_db_paths(cno):
     """db comes from the backward kernel itself in a first-order backward (one launch) and from the differentiable dx.sum when
     a graph is requested (filtered_lrelu.py:257-258); both must agree with the oracle, and d(db)/d(dy) must exist."""

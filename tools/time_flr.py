@@ -32,7 +32,7 @@ def main():
     zb = torch.zeros(C, device=dev, dtype=dt)
     dbt = torch.zeros(C, device=dev) if os.environ.get('TIME_DB') else None
     def bwd(i):
-        return plug.filtered_lrelu(dys[i % len(dys)], fd, fu, zb, so_, down, up, pp[0], pp[1], pp[2], pp[3], px0 - (tu - 1), py0 - (tu - 1), gg, slope, float('inf'), True, False, db=dbt)
+        return plug.filtered_lrelu(dys[i % len(dys)], fd, fu, zb, so_, down, up, pp[0], pp[1], pp[2], pp[3], px0 - (tu - 1), py0 - (tu - 1), gg, slope, float('inf'), True, False, db=dbt, signs_only=not os.environ.get('TIME_CLAMPBITS'))
     assert bwd(0)[2] == 0
     res = {}
     for name, fn in (('fwd', fwd), ('bwd', bwd)):
