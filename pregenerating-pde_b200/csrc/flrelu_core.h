@@ -297,14 +297,22 @@ struct Stream {
         } else {
             if (MODE == SIGN_WRITE) {
                 // sign bits of four floats -> bits 0, 2, 4, 6: one shift + three funnel shifts + shift + and
+#ifndef FLR_X_NOPACK
                 uint32_t r = f_bits(v[1].y) >> 30;
                 r = funnel_l(f_bits(v[1].x), r, 2); r = funnel_l(f_bits(v[0].y), r, 2); r = funnel_l(f_bits(v[0].x), r, 2);
                 code = (r >> 1) & colmask;
+#else
+                code = f_bits(v[0].x) >> 31;
+#endif
             }
             // lrelu(v) = max(v, slope*v); the host plan only admits 0 <= slope <= 1
             const f2 sl = mk2(p.slope, p.slope), z = mk2(0.f, 0.f);
             const f2 s0 = ffma2(v[0], sl, z), s1 = ffma2(v[1], sl, z);
+#ifndef FLR_X_NOMAX
             v[0] = mk2(fmaxf(v[0].x, s0.x), fmaxf(v[0].y, s0.y)); v[1] = mk2(fmaxf(v[1].x, s1.x), fmaxf(v[1].y, s1.y));
+#else
+            v[0] = s0; v[1] = s1;
+#endif
         }
     }
 
@@ -342,7 +350,8 @@ struct Stream {
             }
             act(p, v, code);
 #ifndef FLR_X_NOMASK
-            if (MODE == SIGN_WRITE) { if (j < p.UH) mrow0[(int64_t)j * p.mask_pitch] = (uint8_t)code; }
+            // 32-bit row offset (uniform across the CTA: one UIMAD, no per-thread 64-bit address arithmetic)
+            if (MODE == SIGN_WRITE) { if (j < p.UH) mrow0[(uint32_t)(j * p.mask_pitch)] = (uint8_t)code; }
 #else
             if (MODE == SIGN_WRITE) { if (j < p.UH && code == 0x12345u) mrow0[(int64_t)j * p.mask_pitch] = (uint8_t)code; }
 #endif
