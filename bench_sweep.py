@@ -190,6 +190,7 @@ def main():
             sweep_bias_act(rows, N, C, H, dt, reps)
         for C, H in levels + [(64, 128)]:
             sweep_cin(rows, N, C, H, dt, reps)
+        sweep_cin(rows, 8, 64, 256, dt, reps)                                 # wide fine-tune planes: thread-block cluster kernels
     out = dict(gpu=torch.cuda.get_device_name(0), hbm_peak_gbs=peak(), rows=rows)
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     json.dump(out, open(args.out, 'w'), indent=1)

@@ -6,7 +6,10 @@
 // time conditioning is applied from registers, so HBM sees x exactly once (and dy once in backward).
 // Planes that do not fit (hw not a multiple of the vector width, or > GS*VPT vectors) take the
 // streaming path (three sweeps, second and third from L2).
+#include <stdlib.h>
 #include "common.cuh"
+#include <cooperative_groups.h>
+namespace cgrp = cooperative_groups;
 
 namespace {
 
@@ -208,6 +211,158 @@ __global__ void __launch_bounds__(1024) cin_bwd_reg_kernel(CinParams p) {
     }
 }
 
+// ---- planes larger than one CTA's registers (256^2: the wide fine-tune configuration): a thread-block CLUSTER holds the plane --
+// CS CTAs of 512 threads each keep 1/CS of the plane in registers; the statistics are reduced inside each CTA (shuffles + one
+// shared-memory hop) and the CS partial results are exchanged through distributed shared memory, so x (and dy) still cross HBM
+// exactly once.  One exchange per kernel; the closing cluster barrier (arrive right after the remote reads, wait before exit)
+// keeps a CTA's shared memory alive until its peers have read it and overlaps with the store phase.
+constexpr int CLUSTER_CTA = 512;
+
+__device__ __forceinline__ void cluster_sum2(cgrp::cluster_group& cluster, float& a, float& b, float2* part, float* red, int round) {
+    group_sum2(a, b, (int)blockDim.x, red, round);             // CTA totals in every thread
+    if (threadIdx.x == 0) part[round] = make_float2(a, b);
+    cluster.sync();
+    float sa = 0.f, sb = 0.f;
+    const unsigned cs = cluster.num_blocks();
+    for (unsigned r = 0; r < cs; r++) {                         // same order in every CTA: identical results
+        const float2 v = *cluster.map_shared_rank(&part[round], r);
+        sa += v.x; sb += v.y;
+    }
+    a = sa; b = sb;
+    cluster.barrier_arrive();                                   // done reading the peers: the matching barrier_wait() sits at the kernel's end
+}
+
+template <class T, int VPT>
+__global__ void __launch_bounds__(CLUSTER_CTA, 2) cin_fwd_cluster_kernel(CinParams p) {
+    constexpr int V = Pack<T>::V;
+    __shared__ float red[8 * 32];
+    __shared__ float2 part[2];
+    cgrp::cluster_group cluster = cgrp::this_cluster();
+    const int cs = (int)cluster.num_blocks(), rank = (int)cluster.block_rank();
+    const int64_t plane = blockIdx.x / cs;
+    const int gs = cs * CLUSTER_CTA, t = rank * CLUSTER_CTA + threadIdx.x;
+    const int nvec = p.hw / V;
+    const T* xp = (const T*)p.x + plane * (int64_t)p.hw;
+    uint4 v[VPT];
+#pragma unroll
+    for (int k = 0; k < VPT; k++) {
+        const int i = t + k * gs;
+        v[k] = i < nvec ? ldg16_stream(xp + (int64_t)i * V) : make_uint4(0u, 0u, 0u, 0u);
+    }
+    float s = 0.f, q = 0.f;                                     // conditioning: every CTA of the cluster computes it (tiny)
+    if (p.film.t) film_affine(p, true, plane, threadIdx.x, CLUSTER_CTA, red, s, q);
+    else { s = p.scale[plane]; q = p.shift[plane]; }
+    // statistics with ONE cluster exchange: every CTA reduces its own part to (sum_r, M2_r about its own mean) with two cheap
+    // CTA-level reductions, the cluster exchanges the pairs, and the parts are combined with the pairwise-variance identity
+    //   M2 = sum_r [ M2_r + n_r * (mean_r - mu)^2 ]      (exact; no E[x^2] - mu^2 cancellation)
+    float sum = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPT; k++) {
+        float f[V]; Pack<T>::get(v[k], f);
+#pragma unroll
+        for (int e = 0; e < V; e++) sum += f[e];
+    }
+    sum = group_sum(sum, CLUSTER_CTA, red, 0);
+    auto count_of = [&](int rk) {                              // elements held by CTA rk
+        int n = 0;
+        for (int k = 0; k < VPT; k++) { const int m = nvec - k * gs - rk * CLUSTER_CTA; n += m < 0 ? 0 : (m > CLUSTER_CTA ? CLUSTER_CTA : m); }
+        return n * V;
+    };
+    const int n_mine = count_of(rank);
+    const float mean_mine = n_mine > 0 ? sum / (float)n_mine : 0.f;
+    float sq = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPT; k++) {
+        if (t + k * gs < nvec) {
+            float f[V]; Pack<T>::get(v[k], f);
+#pragma unroll
+            for (int e = 0; e < V; e++) { const float d = f[e] - mean_mine; sq = fmaf(d, d, sq); }
+        }
+    }
+    sq = group_sum(sq, CLUSTER_CTA, red, 1);
+    if (threadIdx.x == 0) part[0] = make_float2(sum, sq);
+    cluster.sync();
+    float tot = 0.f, m2 = 0.f;
+    float2 pr[8];
+#pragma unroll
+    for (int rk = 0; rk < 8; rk++) { pr[rk] = rk < cs ? *cluster.map_shared_rank(&part[0], rk) : make_float2(0.f, 0.f); tot += pr[rk].x; }
+    cluster.barrier_arrive();                                   // done reading the peers; waited for before exit (split phase)
+    const float inv_hw = 1.f / (float)p.hw;
+    const float mu = tot * inv_hw;
+#pragma unroll
+    for (int rk = 0; rk < 8; rk++) {
+        if (rk < cs) {
+            const int n = count_of(rk);
+            const float dm = (n > 0 ? pr[rk].x / (float)n : mu) - mu;
+            m2 += pr[rk].y + (float)n * dm * dm;
+        }
+    }
+    const float r = rsqrtf(m2 * inv_hw + p.eps);
+    const int ch = (int)(plane % p.c);
+    const float a = p.gamma[ch] * s * r;
+    const float d0 = p.beta[ch] * s + q - mu * a;
+    if (t == 0) { p.mean[plane] = mu; p.rstd[plane] = r; }
+    T* yp = (T*)p.y + plane * (int64_t)p.hw;
+#pragma unroll
+    for (int k = 0; k < VPT; k++) {
+        const int i = t + k * gs;
+        if (i < nvec) {
+            float f[V]; Pack<T>::get(v[k], f);
+#pragma unroll
+            for (int e = 0; e < V; e++) f[e] = fmaf(f[e], a, d0);
+            *reinterpret_cast<uint4*>(yp + (int64_t)i * V) = Pack<T>::put(f);
+        }
+    }
+    cluster.barrier_wait();                                     // a CTA's shared memory must outlive its peers' reads
+}
+
+template <class T, int VPT>
+__global__ void __launch_bounds__(CLUSTER_CTA, 2) cin_bwd_cluster_kernel(CinParams p) {
+    constexpr int V = Pack<T>::V;
+    __shared__ float red[8 * 32];
+    __shared__ float2 part[2];
+    cgrp::cluster_group cluster = cgrp::this_cluster();
+    const int cs = (int)cluster.num_blocks(), rank = (int)cluster.block_rank();
+    const int64_t plane = blockIdx.x / cs;
+    const int gs = cs * CLUSTER_CTA, t = rank * CLUSTER_CTA + threadIdx.x;
+    const int nvec = p.hw / V;
+    const int64_t base = plane * (int64_t)p.hw;
+    const T* xp = (const T*)p.x + base; const T* gp = (const T*)p.dy + base;
+    uint4 vx[VPT], vg[VPT];
+#pragma unroll
+    for (int k = 0; k < VPT; k++) {
+        const int i = t + k * gs;
+        vx[k] = i < nvec ? ldg16_stream(xp + (int64_t)i * V) : make_uint4(0u, 0u, 0u, 0u);
+        vg[k] = i < nvec ? ldg16_stream(gp + (int64_t)i * V) : make_uint4(0u, 0u, 0u, 0u);
+    }
+    const float mu = p.mean[plane], r = p.rstd[plane];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPT; k++) {
+        float fx[V], fg[V]; Pack<T>::get(vx[k], fx); Pack<T>::get(vg[k], fg);
+#pragma unroll
+        for (int e = 0; e < V; e++) { s1 += fg[e]; s2 = fmaf(fg[e], (fx[e] - mu) * r, s2); }
+    }
+    cluster_sum2(cluster, s1, s2, part, red, 0);
+    const int ch = (int)(plane % p.c);
+    if (t == 0) { p.s1[plane] = s1; p.s2[plane] = s2; }
+    const float inv_hw = 1.f / (float)p.hw;
+    const float a = p.gamma[ch] * p.scale[plane] * r;
+    const float m1 = s1 * inv_hw, m2 = s2 * inv_hw;
+    T* dp = (T*)p.y + base;
+#pragma unroll
+    for (int k = 0; k < VPT; k++) {
+        const int i = t + k * gs;
+        if (i < nvec) {
+            float fx[V], fg[V]; Pack<T>::get(vx[k], fx); Pack<T>::get(vg[k], fg);
+#pragma unroll
+            for (int e = 0; e < V; e++) fg[e] = a * (fg[e] - m1 - (fx[e] - mu) * r * m2);
+            *reinterpret_cast<uint4*>(dp + (int64_t)i * V) = Pack<T>::put(fg);
+        }
+    }
+    cluster.barrier_wait();                                     // a CTA's shared memory must outlive its peers' reads
+}
+
 // streaming path: one CTA per plane, any hw
 template <class T, bool BWD>
 __global__ void __launch_bounds__(CTA) cin_stream_kernel(CinParams p) {
@@ -362,6 +517,20 @@ int cin_launch(CinParams p, cudaStream_t st) {
         const int64_t blocks = (p.planes + ppc - 1) / ppc;
         if constexpr (BWD) cin_bwd_reg_kernel<T, VPT><<<(unsigned)blocks, threads, 0, st>>>(p);
         else cin_fwd_reg_kernel<T, VPT><<<(unsigned)blocks, threads, 0, st>>>(p);
+    } else if (vec_ok && (int64_t)8 * CLUSTER_CTA * VPT >= nvec && p.planes * 8 < (1ll << 31) && !getenv("CNO_CIN_NO_CLUSTER")) {
+        // thread-block cluster of 2 / 4 / 8 CTAs per plane (portable cluster size limit: 8)
+        int cs = 2;
+        while ((int64_t)cs * CLUSTER_CTA * VPT < nvec) cs <<= 1;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(p.planes * cs)); cfg.blockDim = dim3(CLUSTER_CTA); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+        cudaLaunchAttribute attr;
+        attr.id = cudaLaunchAttributeClusterDimension;
+        attr.val.clusterDim.x = (unsigned)cs; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+        cfg.attrs = &attr; cfg.numAttrs = 1;
+        cudaError_t e;
+        if constexpr (BWD) e = cudaLaunchKernelEx(&cfg, cin_bwd_cluster_kernel<T, VPT>, p);
+        else e = cudaLaunchKernelEx(&cfg, cin_fwd_cluster_kernel<T, VPT>, p);
+        if (e != cudaSuccess) { cno_set_error("cin: cluster launch failed: %s", cudaGetErrorString(e)); return (int)e; }
     } else {
         cin_stream_kernel<T, BWD><<<(unsigned)p.planes, CTA, 0, st>>>(p);
     }

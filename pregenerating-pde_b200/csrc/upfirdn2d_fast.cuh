@@ -73,6 +73,12 @@ struct Geo {
     static_assert(TOW % F::R == 0 && TOH % F::R == 0 && THREADS % TOW == 0, "tile / strip / thread shapes");
 };
 
+// two packed 16-bit elements -> fp32 (low half = lower address)
+template <class T> __device__ __forceinline__ float2 unpack2(uint32_t w);
+template <> __device__ __forceinline__ float2 unpack2<__nv_bfloat16>(uint32_t w) { return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u)); }
+template <> __device__ __forceinline__ float2 unpack2<__half>(uint32_t w) { return __half22float2(*reinterpret_cast<const __half2*>(&w)); }
+template <> __device__ __forceinline__ float2 unpack2<float>(uint32_t) { return make_float2(0.f, 0.f); }   // never used
+
 template <class T, int UP, int DOWN, int NT, bool SMALL>
 __global__ void __launch_bounds__(Geo<UP, DOWN, NT, SMALL>::THREADS)
 upfirdn2d_fast_kernel(const Params p) {
@@ -96,9 +102,42 @@ upfirdn2d_fast_kernel(const Params p) {
     if (tid < 2 * NT) { const int a = tid < NT ? 0 : NT, t = tid - a; s_f[tid] = p.f[a + (p.flip ? t : NT - 1 - t)]; }
 
     // ---- stage: footprint -> s_in ------------------------------------------------------------------
-    {
-        const T* xp = (const T*)p.x + (size_t)plane * p.in_h * p.in_w;
-        const int warp = tid >> 5, lane = tid & 31;
+    const T* xp = (const T*)p.x + (size_t)plane * p.in_h * p.in_w;
+    const int warp = tid >> 5, lane = tid & 31;
+    if (sizeof(T) == 2 && (p.in_w & 1) == 0 && ((uintptr_t)p.x & 3u) == 0) {
+        // 16-bit elements: 4-byte loads of element pairs (even source column first), a warp covers 64 columns per load;
+        // an even plane width keeps every pair inside one row and either both or none of its elements inside the plane
+        constexpr int K2 = (G::ITW + 1 + 63) / 64, RB = 4;
+        const int e = ibx & 1;                                   // the pair of lane 0 starts one column left of the footprint when ibx is odd
+        unsigned cmask = 0;
+#pragma unroll
+        for (int k = 0; k < K2; k++) { const int sx = ibx - e + 2 * lane + 64 * k; if (sx >= 0 && sx < p.in_w) cmask |= 1u << k; }
+        for (int r = warp; r < ITH; r += RB * NW) {
+            uint32_t v[RB][K2];
+#pragma unroll
+            for (int u = 0; u < RB; u++) {
+                const int sy = iby + r + u * NW;
+                const bool rok = sy >= 0 && sy < p.in_h && r + u * NW < ITH;
+                const T* xr = xp + (size_t)(rok ? sy : 0) * p.in_w + (ibx - e + 2 * lane);
+#pragma unroll
+                for (int k = 0; k < K2; k++)
+                    v[u][k] = (rok && ((cmask >> k) & 1u)) ? *reinterpret_cast<const uint32_t*>(xr + 64 * k) : 0u;
+            }
+#pragma unroll
+            for (int u = 0; u < RB; u++) {
+                if (r + u * NW < ITH) {
+#pragma unroll
+                    for (int k = 0; k < K2; k++) {
+                        const int c = 2 * lane + 64 * k - e;
+                        const float2 f = unpack2<T>(v[u][k]);
+                        float* dst = s_in + (r + u * NW) * PIN + c;
+                        if (c >= 0 && c < PIN) dst[0] = f.x;
+                        if (c + 1 < PIN) dst[1] = f.y;
+                    }
+                }
+            }
+        }
+    } else {
         unsigned cmask = 0;              // bit k: column lane + 32k lies inside the plane
 #pragma unroll
         for (int k = 0; k < G::K; k++) { const int sx = ibx + lane + 32 * k; if (sx >= 0 && sx < p.in_w) cmask |= 1u << k; }

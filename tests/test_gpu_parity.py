@@ -289,7 +289,8 @@ def test_upfirdn2d_full_size_adjoint(cno, shape, f_taps, kw):
 
 @pytest.mark.parametrize('up,down,taps', [(1, 1, 4), (1, 1, 12), (2, 1, 4), (2, 1, 8), (2, 1, 12), (2, 1, 16), (2, 1, 24), (4, 1, 4),
                                           (4, 1, 24), (4, 1, 16), (1, 2, 4), (1, 2, 12), (1, 2, 24), (1, 4, 8), (1, 4, 24)])
-@pytest.mark.parametrize('shape,pad', [((2, 3, 37, 53), [3, 2, 5, 1]), ((1, 2, 150, 141), [-1, 7, 0, -2]), ((3, 2, 8, 8), [6, 5, 6, 5])])
+@pytest.mark.parametrize('shape,pad', [((2, 3, 37, 53), [3, 2, 5, 1]), ((1, 2, 150, 141), [-1, 7, 0, -2]), ((3, 2, 8, 8), [6, 5, 6, 5]),
+                                       ((2, 2, 40, 160), [3, 2, 5, 1]), ((1, 3, 66, 72), [-2, 5, 1, 0])])
 def test_upfirdn2d_fast_path(cno, up, down, taps, shape, pad):
     """register-window kernel (csrc/upfirdn2d_fast.cuh): asymmetric random taps (flip conventions matter), odd plane sizes that
     leave partial tiles and strips, positive and negative padding; vs the oracle and vs the generic kernel."""
@@ -430,6 +431,36 @@ def test_cin_sizes(cno, N, C, S, dtype):
     assert rel(y, y_ref) < tol
     for a, r in zip(g_got, g_ref):
         assert rel(a, r) < (1e-4 if dtype == torch.float32 else 3e-2)
+
+
+@pytest.mark.parametrize('S,dtype', [(256, torch.float32), (192, torch.float32), (200, torch.float32), (256, torch.bfloat16), (360, torch.bfloat16)])
+def test_cin_cluster_path(cno, S, dtype):
+    """planes that do not fit one CTA's registers are held by a thread-block cluster (partial statistics exchanged through
+    distributed shared memory): same results as the oracle and as the three-sweep streaming kernel."""
+    import os
+    N, C = 2, 5
+    g = torch.Generator().manual_seed(S)
+    x = (torch.randn(N, C, S, S, generator=g) * 1.5 + 0.3).to(dtype)
+    gamma, beta = torch.randn(C, generator=g), torch.randn(C, generator=g)
+    scale, shift = torch.randn(N, C, generator=g), torch.randn(N, C, generator=g)
+    dy = torch.randn(N, C, S, S, generator=g).to(dtype)
+    leaves = [t.clone().requires_grad_(True) for t in (x.float(), gamma, beta, scale, shift)]
+    y_ref = O.cin(*leaves)
+    g_ref = torch.autograd.grad(y_ref, leaves, dy.float())
+
+    def run():
+        dl = [x.to(DEV).requires_grad_(True)] + [t.to(DEV).requires_grad_(True) for t in (gamma, beta, scale, shift)]
+        y = cno.cin.cin(*dl)
+        return [y] + list(torch.autograd.grad(y, dl, dy.to(DEV)))
+    got = run()
+    os.environ['CNO_CIN_NO_CLUSTER'] = '1'
+    try:
+        stream = run()
+    finally:
+        del os.environ['CNO_CIN_NO_CLUSTER']
+    tol = 2e-5 if dtype == torch.float32 else 2e-2
+    for a, b_, r in zip(got, stream, [y_ref] + list(g_ref)):
+        assert rel(a, r) < (5 * tol) and rel(a, b_) < (5 * tol)
 
 
 def test_plugin_layer_matches_reference_signatures(cno):
