@@ -14,6 +14,7 @@ bottleneck, BatchNorm / LayerNorm flavours and the alternative activations are o
 """
 import numpy as np
 import scipy.signal
+import scipy.special
 import torch
 from torch import nn
 
@@ -28,7 +29,6 @@ class LReLu(nn.Module):
                  in_cutoff, out_cutoff, in_half_width, out_half_width, filter_size=6, lrelu_upsampling=2,
                  is_critically_sampled=False, use_radial_filters=False, impl='cuda'):
         super().__init__()
-        assert not use_radial_filters, 'radial filters are outside the CNO configurations (SURVEY §8f-4)'
         self.in_channels, self.out_channels = in_channels, out_channels
         self.in_size = np.broadcast_to(np.asarray(in_size), [2])
         self.out_size = np.broadcast_to(np.asarray(out_size), [2])
@@ -40,7 +40,9 @@ class LReLu(nn.Module):
         self.register_buffer('up_filter', self.design_lowpass_filter(self.up_taps, in_cutoff, in_half_width * 2, self.tmp_sampling_rate))
         self.down_factor = int(np.rint(self.tmp_sampling_rate / out_sampling_rate))
         self.down_taps = filter_size * self.down_factor if self.down_factor > 1 else 1
-        self.register_buffer('down_filter', self.design_lowpass_filter(self.down_taps, out_cutoff, out_half_width * 2, self.tmp_sampling_rate))
+        self.down_radial = bool(use_radial_filters) and not is_critically_sampled            # filtered_networks.py:245
+        self.register_buffer('down_filter', self.design_lowpass_filter(self.down_taps, out_cutoff, out_half_width * 2, self.tmp_sampling_rate,
+                                                                       radial=self.down_radial))
         # padding of the up-sampled signal (filtered_networks.py:254-262)
         total = (self.out_size - 1) * self.down_factor + 1 - self.in_size * self.up_factor + self.up_taps + self.down_taps - 2
         lo = (total + self.up_factor) // 2
@@ -48,10 +50,19 @@ class LReLu(nn.Module):
         self.padding = [int(lo[0]), int(hi[0]), int(lo[1]), int(hi[1])]
 
     @staticmethod
-    def design_lowpass_filter(numtaps, cutoff, width, fs):
+    def design_lowpass_filter(numtaps, cutoff, width, fs, radial=False):
+        """Kaiser low-pass taps (separable) or the radially symmetric jinc filter [numtaps, numtaps]
+        (filtered_networks.py:280-301); a 2-D down filter takes the generic composition instead of the fused kernel."""
         if numtaps == 1:
             return None
-        return torch.as_tensor(scipy.signal.firwin(numtaps=numtaps, cutoff=cutoff, width=width, fs=fs), dtype=torch.float32)
+        if not radial:
+            return torch.as_tensor(scipy.signal.firwin(numtaps=numtaps, cutoff=cutoff, width=width, fs=fs), dtype=torch.float32)
+        pos = (np.arange(numtaps) - (numtaps - 1) / 2) / fs
+        rad = np.hypot(*np.meshgrid(pos, pos))
+        f = scipy.special.j1(2 * cutoff * (np.pi * rad)) / (np.pi * rad)
+        win = np.kaiser(numtaps, scipy.signal.kaiser_beta(scipy.signal.kaiser_atten(numtaps, width / (fs / 2))))
+        f *= np.outer(win, win)
+        return torch.as_tensor(f / np.sum(f), dtype=torch.float32)
 
     def forward(self, x):
         y = filtered_lrelu.filtered_lrelu(x=x, fu=self.up_filter, fd=self.down_filter, b=self.bias.to(x.dtype), up=self.up_factor,

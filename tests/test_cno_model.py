@@ -110,3 +110,31 @@ def test_mirror_key_set_full_config():
     b = cno_model.CNO_time(**cfg).state_dict()
     assert {k: tuple(v.shape) for k, v in a.items()} == {k: tuple(v.shape) for k, v in b.items()}
     assert sum(v.numel() for k, v in cno_model.CNO_time(**cfg).named_parameters()) == 18280147
+
+
+# ---- radial (jinc) down filter flavour of LReLu: golden vectors from the unmodified reference LReLu -------------
+def _radial_case(golden, name, dev):
+    from pregenerating_pde_b200 import cno_model
+    g = golden['lrelu_radial']
+    si, so = {'I': (16, 16), 'D': (16, 8), 'U': (8, 16)}[name]
+    m = cno_model.lrelu_for(3, si, so, use_radial_filters=True).to(dev)
+    assert m.down_filter.ndim == 2 and m.padding == [int(v) for v in g[f'{name}.padding']]
+    assert _rel(m.up_filter, g[f'{name}.fu']) < 1e-6 and _rel(m.down_filter, g[f'{name}.fd']) < 1e-6
+    with torch.no_grad():
+        m.bias.copy_(torch.from_numpy(g[f'{name}.b']))
+    x = torch.from_numpy(g[f'{name}.x']).to(dev).requires_grad_(True)
+    y = m(x)
+    dx, db = torch.autograd.grad(y, [x, m.bias], torch.from_numpy(g[f'{name}.dy']).to(dev))
+    assert _rel(y, g[f'{name}.y']) < 1e-5 and _rel(dx, g[f'{name}.dx']) < 1e-5 and _rel(db, g[f'{name}.db']) < 1e-5
+
+
+@pytest.mark.parametrize('name', ['I', 'D', 'U'])
+def test_lrelu_radial_filters_cpu(golden, name):
+    _radial_case(golden, name, 'cpu')
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('name', ['I', 'D', 'U'])
+def test_lrelu_radial_filters_gpu(golden, name):
+    """2-D down filter: no fused variant -> generic composition (fast separable up pass, act kernel, generic 2-D down pass)"""
+    _radial_case(golden, name, 'cuda')

@@ -14,4 +14,7 @@ done
 CMD="python tools/time_cin.py 32 64 128 f32 6"
 timeout 120 $CMD > gpurun_out/plain_cin.log 2>&1 && \
 timeout 500 ncu --set full --clock-control none --import-source on -k regex:cin_ -s 6 -c 2 -f -o gpurun_out/r1_cin $CMD > gpurun_out/ncu_cin.log 2>&1
+CMD="python tools/time_cin.py 8 64 256 f32 6"
+timeout 120 $CMD > gpurun_out/plain_cin256.log 2>&1 && \
+timeout 500 ncu --set full --clock-control none --import-source on -k regex:cin_ -s 6 -c 2 -f -o gpurun_out/r1_cin256 $CMD > gpurun_out/ncu_cin256.log 2>&1
 ls -la gpurun_out/*.ncu-rep
