@@ -99,6 +99,17 @@ int cno_film_fwd(const void* x, void* y, const float* t, const float* gamma, con
                  const float* w1b, const float* b1b, const float* W2b, const float* b2b,
                  float* scale_out, float* mean, float* rstd, int dtype, int n, int c, int hw, int lat,
                  float eps, void* stream);
+/* ResidualBlock epilogue (CNO_timeModule_CIN.py:503-507, `x + in_norm_conditiner2(out, time)`): the same two forward kernels with
+ * `y = residual + CIN(x)` written in the one pass; residual has the layout and dtype of x.  residual = NULL is cno_cin_fwd /
+ * cno_film_fwd.  The backward needs nothing new: d residual = dy, and cno_cin_bwd is unchanged. */
+int cno_cin_fwd_res(const void* x, const void* residual, void* y, const float* gamma, const float* beta, const float* scale,
+                    const float* shift, float* mean, float* rstd, int dtype, int n, int c, int hw, float eps, void* stream);
+int cno_film_fwd_res(const void* x, const void* residual, void* y, const float* t, const float* gamma, const float* beta,
+                     const float* w1s, const float* b1s, const float* W2s, const float* b2s,
+                     const float* w1b, const float* b1b, const float* W2b, const float* b2b,
+                     float* scale_out, float* mean, float* rstd, int dtype, int n, int c, int hw, int lat,
+                     float eps, void* stream);
+
 /* every parameter gradient of one FILM module from the per-plane sums s1, s2 of cno_cin_bwd, in one launch
  * (replaces autograd through 4 Linear layers, ~20 small kernels): dgamma, dbeta [C]; d lat2scale.weight [C,lat] / bias [C];
  * d inp2lat_sacale.weight / bias [lat]; the same four for the shift branch.  Deterministic (no atomics). */

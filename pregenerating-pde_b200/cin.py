@@ -16,17 +16,18 @@ FUSE_LINEARS = True       # False: keep the four Linear layers in torch (autogra
 
 class _Cin(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, scale, shift, eps):
+    def forward(ctx, x, gamma, beta, scale, shift, eps, res=None):
         lib = _lib.load()
         n, c, h, w = x.shape
         x = x.contiguous()
+        res = None if res is None else res.to(x.dtype).contiguous()
         g32, b32 = gamma.detach().float().contiguous(), beta.detach().float().contiguous()
         s32, q32 = scale.detach().float().contiguous(), shift.detach().float().contiguous()
         y = torch.empty_like(x)
         mean = torch.empty([n, c], dtype=torch.float32, device=x.device)
         rstd = torch.empty_like(mean)
         with torch.cuda.device(x.device):
-            rc = lib.cno_cin_fwd(_ptr(x), _ptr(y), _ptr(g32), _ptr(b32), _ptr(s32), _ptr(q32), _ptr(mean), _ptr(rstd),
+            rc = lib.cno_cin_fwd_res(_ptr(x), _ptr(res), _ptr(y), _ptr(g32), _ptr(b32), _ptr(s32), _ptr(q32), _ptr(mean), _ptr(rstd),
                                  _DT[x.dtype], n, c, h * w, float(eps), _stream(x))
         _lib.check(rc, 'cin_fwd')
         ctx.save_for_backward(x, g32, b32, s32, mean, rstd)
@@ -56,15 +57,17 @@ class _Cin(torch.autograd.Function):
             ds = (g32 * s2 + b32 * s1).to(sd)
         if ctx.needs_input_grad[4]:
             dq = s1.to(qd)
-        return (dx if ctx.needs_input_grad[0] else None), dg, db, ds, dq, None
+        return (dx if ctx.needs_input_grad[0] else None), dg, db, ds, dq, None, (dy if ctx.needs_input_grad[6] else None)
 
 
-def cin(x, gamma, beta, scale, shift, eps=1e-5):
-    """x [N,C,H,W] (fp32 / bf16 / fp16, CUDA); gamma, beta [C]; scale, shift [N,C]."""
+def cin(x, gamma, beta, scale, shift, eps=1e-5, residual=None):
+    """x [N,C,H,W] (fp32 / bf16 / fp16, CUDA); gamma, beta [C]; scale, shift [N,C]; residual (optional, shape of x): returns
+    residual + CIN(x) from the same pass."""
+    assert residual is None or residual.shape == x.shape
     assert x.is_cuda and x.ndim == 4
     assert gamma.shape == (x.shape[1],) and beta.shape == (x.shape[1],)
     assert scale.shape == x.shape[:2] and shift.shape == x.shape[:2]
-    return _Cin.apply(x, gamma, beta, scale, shift, eps)
+    return _Cin.apply(x, gamma, beta, scale, shift, eps, residual)
 
 
 class _Film(torch.autograd.Function):
@@ -72,10 +75,11 @@ class _Film(torch.autograd.Function):
     backward of two kernels (cno_cin_bwd + cno_film_bwd_finish) instead of ~30 small torch launches."""
 
     @staticmethod
-    def forward(ctx, x, t, gamma, beta, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b, eps):
+    def forward(ctx, x, t, gamma, beta, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b, eps, res=None):
         lib = _lib.load()
         n, c, h, w = x.shape
         x = x.contiguous()
+        res = None if res is None else res.to(x.dtype).contiguous()
         f32 = lambda v: v.detach().float().contiguous()
         t32 = f32(t).reshape(-1)
         P = [f32(v) for v in (gamma, beta, w1s.reshape(-1), b1s, W2s, b2s, w1b.reshape(-1), b1b, W2b, b2b)]
@@ -85,7 +89,7 @@ class _Film(torch.autograd.Function):
         mean = torch.empty([n, c], dtype=torch.float32, device=x.device)
         rstd, scale = torch.empty_like(mean), torch.empty_like(mean)
         with torch.cuda.device(x.device):
-            rc = lib.cno_film_fwd(_ptr(x), _ptr(y), _ptr(t32), *[_ptr(v) for v in P], _ptr(scale), _ptr(mean), _ptr(rstd),
+            rc = lib.cno_film_fwd_res(_ptr(x), _ptr(res), _ptr(y), _ptr(t32), *[_ptr(v) for v in P], _ptr(scale), _ptr(mean), _ptr(rstd),
                                   _DT[x.dtype], n, c, h * w, lat, float(eps), _stream(x))
         _lib.check(rc, 'film_fwd')
         ctx.save_for_backward(x, t32, scale, mean, rstd, *P)
@@ -117,7 +121,7 @@ class _Film(torch.autograd.Function):
             _lib.check(rc, 'film_bwd_finish')
         outs = [gi.view(shape).to(dt) for gi, (dt, shape) in zip(g, ctx.meta)]
         outs = [o if need else None for o, need in zip(outs, ctx.needs_input_grad[2:12])]
-        return (dx if ctx.needs_input_grad[0] else None, None, *outs, None)
+        return (dx if ctx.needs_input_grad[0] else None, None, *outs, None, dy if ctx.needs_input_grad[13] else None)
 
 
 def _film_fusable(self, x):
@@ -128,20 +132,22 @@ def _film_fusable(self, x):
             and all(m.weight.dtype == torch.float32 for m in lin) and not torch.is_autocast_enabled())
 
 
-def film_forward(self, x, timestep):
+def film_forward(self, x, timestep, residual=None):
     """Replacement for FILM.forward (CNO_timeModule_CIN.py:60-70).  Uses the fused kernel when the module
-    is the instance-norm flavour on a CUDA tensor; every other case runs the module's own torch ops."""
+    is the instance-norm flavour on a CUDA tensor; every other case runs the module's own torch ops.
+    residual (extension): returns residual + FILM(x), added in the kernel's single pass (ResidualBlock epilogue, :503-507)."""
     norm = self.norm
     fused = (x.is_cuda and x.ndim == 4 and isinstance(norm, torch.nn.InstanceNorm2d) and norm.affine
              and not norm.track_running_stats and x.dtype in _DT and x.dtype != torch.float64)
     if fused and FUSE_LINEARS and _film_fusable(self, x) and not timestep.requires_grad:
         return _Film.apply(x, timestep, norm.weight, norm.bias, self.inp2lat_sacale.weight, self.inp2lat_sacale.bias,
                            self.lat2scale.weight, self.lat2scale.bias, self.inp2lat_bias.weight, self.inp2lat_bias.bias,
-                           self.lat2bias.weight, self.lat2bias.bias, norm.eps)
+                           self.lat2bias.weight, self.lat2bias.bias, norm.eps, residual)
     t = timestep.reshape(-1, 1).to(self.inp2lat_sacale.weight.dtype)     # the reference casts to x.dtype (:63), which only works for fp32 x
     scale = self.lat2scale(self.inp2lat_sacale(t))
     shift = self.lat2bias(self.inp2lat_bias(t))
     if fused:
-        return cin(x, norm.weight, norm.bias, scale, shift, norm.eps)
+        return cin(x, norm.weight, norm.bias, scale, shift, norm.eps, residual)
     x = norm(x)
-    return x * scale.unsqueeze(2).unsqueeze(3) + shift.unsqueeze(2).unsqueeze(3)
+    y = x * scale.unsqueeze(2).unsqueeze(3) + shift.unsqueeze(2).unsqueeze(3)
+    return y if residual is None else residual + y

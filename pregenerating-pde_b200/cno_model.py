@@ -157,7 +157,7 @@ class ResidualBlock(nn.Module):
             out = self.in_norm_conditiner1(out, time)
         out = self.convolution2(self.activation(out))
         if self.is_time:
-            out = self.in_norm_conditiner2(out, time)
+            return self.in_norm_conditiner2(out, time, residual=x)      # x + CIN(out) in the CIN kernel's single pass
         return x + out
 
 

@@ -96,6 +96,7 @@ struct FilmW {
 
 struct CinParams {
     const void* x; const void* dy; void* y;
+    const void* res;                         // forward only, optional: y = res + CIN(x)  (ResidualBlock epilogue, CNO_timeModule_CIN.py:503-507)
     const float *gamma, *beta, *scale, *shift;
     float *mean, *rstd, *s1, *s2;
     int64_t planes; int c, hw, gs; float eps;
@@ -159,6 +160,11 @@ __global__ void __launch_bounds__(1024) cin_fwd_reg_kernel(CinParams p) {
             float f[V]; Pack<T>::get(v[k], f);
 #pragma unroll
             for (int e = 0; e < V; e++) f[e] = fmaf(f[e], a, d0);
+            if (p.res) {
+                float rr[V]; Pack<T>::get(ldg16_stream((const T*)p.res + plane * (int64_t)p.hw + (int64_t)i * V), rr);
+#pragma unroll
+                for (int e = 0; e < V; e++) f[e] += rr[e];
+            }
             *reinterpret_cast<uint4*>(yp + (int64_t)i * V) = Pack<T>::put(f);
         }
     }
@@ -310,6 +316,11 @@ __global__ void __launch_bounds__(CLUSTER_CTA, 2) cin_fwd_cluster_kernel(CinPara
             float f[V]; Pack<T>::get(v[k], f);
 #pragma unroll
             for (int e = 0; e < V; e++) f[e] = fmaf(f[e], a, d0);
+            if (p.res) {
+                float rr[V]; Pack<T>::get(ldg16_stream((const T*)p.res + plane * (int64_t)p.hw + (int64_t)i * V), rr);
+#pragma unroll
+                for (int e = 0; e < V; e++) f[e] += rr[e];
+            }
             *reinterpret_cast<uint4*>(yp + (int64_t)i * V) = Pack<T>::put(f);
         }
     }
@@ -385,7 +396,8 @@ __global__ void __launch_bounds__(CTA) cin_stream_kernel(CinParams p) {
         const float a = p.gamma[ch] * s * r, d0 = p.beta[ch] * s + q - mu * a;
         if (threadIdx.x == 0) { p.mean[plane] = mu; p.rstd[plane] = r; }
         T* yp = (T*)p.y + base;
-        for (int i = threadIdx.x; i < p.hw; i += CTA) yp[i] = from_f32<T>(fmaf(to_f32(xp[i]), a, d0));
+        const T* rp = p.res ? (const T*)p.res + base : nullptr;
+        for (int i = threadIdx.x; i < p.hw; i += CTA) yp[i] = from_f32<T>(fmaf(to_f32(xp[i]), a, d0) + (rp ? to_f32(rp[i]) : 0.f));
     } else {
         const T* gp = (const T*)p.dy + base;
         const float mu = p.mean[plane], r = p.rstd[plane];
@@ -506,7 +518,7 @@ int cin_launch(CinParams p, cudaStream_t st) {
     // 16-byte vectors per thread: bounded by the 64 registers a 1024-thread CTA leaves each thread (16-bit types unpack to twice
     // as many fp32 values per vector, so they hold half as many)
     constexpr int VPT = (BWD ? 4 : 8) / (sizeof(T) == 2 ? 2 : 1);
-    const bool vec_ok = (p.hw % V == 0) && !(((uintptr_t)p.x | (uintptr_t)p.y | (uintptr_t)p.dy) & 15u);
+    const bool vec_ok = (p.hw % V == 0) && !(((uintptr_t)p.x | (uintptr_t)p.y | (uintptr_t)p.dy | (uintptr_t)p.res) & 15u);
     const int nvec = p.hw / V;
     int gs = 8;
     while (gs < 1024 && (int64_t)gs * VPT < nvec) gs <<= 1;
@@ -551,13 +563,22 @@ int cin_dispatch(const CinParams& p, int dtype, cudaStream_t st) {
 
 }  // namespace
 
+extern "C" int cno_cin_fwd_res(const void* x, const void* residual, void* y, const float* gamma, const float* beta, const float* scale,
+                               const float* shift, float* mean, float* rstd, int dtype, int n, int c, int hw,
+                               float eps, void* stream);
 extern "C" int cno_cin_fwd(const void* x, void* y, const float* gamma, const float* beta, const float* scale,
                            const float* shift, float* mean, float* rstd, int dtype, int n, int c, int hw,
                            float eps, void* stream) {
+    return cno_cin_fwd_res(x, nullptr, y, gamma, beta, scale, shift, mean, rstd, dtype, n, c, hw, eps, stream);
+}
+
+extern "C" int cno_cin_fwd_res(const void* x, const void* residual, void* y, const float* gamma, const float* beta, const float* scale,
+                               const float* shift, float* mean, float* rstd, int dtype, int n, int c, int hw,
+                               float eps, void* stream) {
     CNO_CHECK_ARG(x && y && gamma && beta && scale && shift && mean && rstd, "cin_fwd: null pointer");
     CNO_CHECK_ARG(n >= 0 && c > 0 && hw > 0, "cin_fwd: bad sizes n=%d c=%d hw=%d", n, c, hw);
     if (n == 0) return 0;
-    CinParams p{}; p.x = x; p.y = y; p.gamma = gamma; p.beta = beta; p.scale = scale; p.shift = shift;
+    CinParams p{}; p.x = x; p.y = y; p.res = residual; p.gamma = gamma; p.beta = beta; p.scale = scale; p.shift = shift;
     p.mean = mean; p.rstd = rstd; p.planes = (int64_t)n * c; p.c = c; p.hw = hw; p.eps = eps;
     return cin_dispatch<false>(p, dtype, (cudaStream_t)stream);
 }
@@ -574,15 +595,29 @@ extern "C" int cno_cin_bwd(const void* x, const void* dy, void* dx, const float*
     return cin_dispatch<true>(p, dtype, (cudaStream_t)stream);
 }
 
+extern "C" int cno_film_fwd_res(const void* x, const void* residual, void* y, const float* t, const float* gamma, const float* beta,
+                                const float* w1s, const float* b1s, const float* W2s, const float* b2s,
+                                const float* w1b, const float* b1b, const float* W2b, const float* b2b,
+                                float* scale_out, float* mean, float* rstd, int dtype, int n, int c, int hw, int lat,
+                                float eps, void* stream);
 extern "C" int cno_film_fwd(const void* x, void* y, const float* t, const float* gamma, const float* beta,
                             const float* w1s, const float* b1s, const float* W2s, const float* b2s,
                             const float* w1b, const float* b1b, const float* W2b, const float* b2b,
                             float* scale_out, float* mean, float* rstd, int dtype, int n, int c, int hw, int lat,
                             float eps, void* stream) {
+    return cno_film_fwd_res(x, nullptr, y, t, gamma, beta, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b, scale_out, mean, rstd, dtype, n, c, hw,
+                            lat, eps, stream);
+}
+
+extern "C" int cno_film_fwd_res(const void* x, const void* residual, void* y, const float* t, const float* gamma, const float* beta,
+                                const float* w1s, const float* b1s, const float* W2s, const float* b2s,
+                                const float* w1b, const float* b1b, const float* W2b, const float* b2b,
+                                float* scale_out, float* mean, float* rstd, int dtype, int n, int c, int hw, int lat,
+                                float eps, void* stream) {
     CNO_CHECK_ARG(x && y && t && gamma && beta && w1s && b1s && W2s && b2s && w1b && b1b && W2b && b2b && mean && rstd, "film_fwd: null pointer");
     CNO_CHECK_ARG(n >= 0 && c > 0 && hw > 0 && lat > 0, "film_fwd: bad sizes n=%d c=%d hw=%d lat=%d", n, c, hw, lat);
     if (n == 0) return 0;
-    CinParams p{}; p.x = x; p.y = y; p.gamma = gamma; p.beta = beta; p.mean = mean; p.rstd = rstd;
+    CinParams p{}; p.x = x; p.y = y; p.res = residual; p.gamma = gamma; p.beta = beta; p.mean = mean; p.rstd = rstd;
     p.planes = (int64_t)n * c; p.c = c; p.hw = hw; p.eps = eps;
     p.film = FilmW{t, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b, scale_out, lat};
     return cin_dispatch<false>(p, dtype, (cudaStream_t)stream);

@@ -9,6 +9,8 @@ fused CIN.  Parameter names / state_dict keys are untouched (SURVEY §5 checkpoi
 import importlib
 import sys
 
+import torch
+
 from .torch_utils import custom_ops as _our_custom_ops
 from . import cin as _cin
 
@@ -34,7 +36,22 @@ def patch_reference(cno_root=None, patch_film=True):
             if 'film_forward' not in _saved:
                 _saved['film_forward'] = film_mod.FILM.forward
             film_mod.FILM.forward = _cin.film_forward
+            if hasattr(film_mod, 'ResidualBlock'):
+                if 'residual_forward' not in _saved:
+                    _saved['residual_forward'] = film_mod.ResidualBlock.forward
+                film_mod.ResidualBlock.forward = _residual_forward
     return True
+
+
+def _residual_forward(self, x, time):
+    """ResidualBlock.forward (CNO_timeModule_CIN.py:496-510) with the closing `x + out` folded into the second CIN's kernel.
+    Any flavour other than time conditioning with Identity batch norms runs the reference's own forward."""
+    timed = self.is_time == 1 or self.is_time is True
+    if not (timed and isinstance(self.batch_norm1, torch.nn.Identity) and isinstance(self.batch_norm2, torch.nn.Identity)):
+        return _saved['residual_forward'](self, x, time)
+    out = self.in_norm_conditiner1(self.convolution1(x), time)
+    out = self.convolution2(self.activation(out))
+    return self.in_norm_conditiner2(out, time, residual=x)
 
 
 def unpatch_reference():
@@ -44,3 +61,5 @@ def unpatch_reference():
             importlib.import_module(f'torch_utils.ops.{name}')._plugin = None
     if 'film_forward' in _saved:
         importlib.import_module('CNO_timeModule_CIN').FILM.forward = _saved.pop('film_forward')
+    if 'residual_forward' in _saved:
+        importlib.import_module('CNO_timeModule_CIN').ResidualBlock.forward = _saved.pop('residual_forward')

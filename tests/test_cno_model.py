@@ -30,11 +30,12 @@ def _rel(a, b):
     return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
 
 
-def _eager_film(self, x, t):
-    """FILM.forward in plain torch ops (CNO_timeModule_CIN.py:60-70)"""
+def _eager_film(self, x, t, residual=None):
+    """FILM.forward in plain torch ops (CNO_timeModule_CIN.py:60-70); residual: the mirror's ResidualBlock epilogue"""
     t = t.reshape(-1, 1).to(x.dtype)
     s, q = self.lat2scale(self.inp2lat_sacale(t)), self.lat2bias(self.inp2lat_bias(t))
-    return self.norm(x) * s[:, :, None, None] + q[:, :, None, None]
+    y = self.norm(x) * s[:, :, None, None] + q[:, :, None, None]
+    return y if residual is None else residual + y
 
 
 def _torch_backend_deviation(golden, dev):

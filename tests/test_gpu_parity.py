@@ -463,6 +463,47 @@ def test_cin_cluster_path(cno, S, dtype):
         assert rel(a, r) < (5 * tol) and rel(a, b_) < (5 * tol)
 
 
+@pytest.mark.parametrize('N,C,S,dtype', [(4, 16, 32, torch.float32), (2, 3, 10, torch.float32), (1, 2, 256, torch.float32), (4, 8, 64, torch.bfloat16)])
+def test_cin_residual_epilogue(cno, N, C, S, dtype):
+    """y = residual + CIN(x) from the forward kernel's single pass (register, streaming and cluster kernels), and the FILM module
+    with residual= against its eager form; d residual = dy."""
+    from pregenerating_pde_b200 import cno_model
+    import copy
+    g = torch.Generator().manual_seed(S * 3 + C)
+    x = (torch.randn(N, C, S, S, generator=g) * 1.5 + 0.3).to(dtype)
+    res = torch.randn(N, C, S, S, generator=g).to(dtype)
+    gamma, beta = torch.randn(C, generator=g), torch.randn(C, generator=g)
+    scale, shift = torch.randn(N, C, generator=g), torch.randn(N, C, generator=g)
+    dy = torch.randn(N, C, S, S, generator=g).to(dtype)
+    leaves = [t.clone().requires_grad_(True) for t in (x.float(), gamma, beta, scale, shift, res.float())]
+    y_ref = O.cin(*leaves[:5]) + leaves[5]
+    g_ref = torch.autograd.grad(y_ref, leaves, dy.float())
+    dl = [x.to(DEV).requires_grad_(True)] + [t.to(DEV).requires_grad_(True) for t in (gamma, beta, scale, shift)] + [res.to(DEV).requires_grad_(True)]
+    y = cno.cin.cin(*dl[:5], residual=dl[5])
+    g_got = torch.autograd.grad(y, dl, dy.to(DEV))
+    tol = 2e-5 if dtype == torch.float32 else 2e-2
+    assert rel(y, y_ref) < tol
+    for a, r in zip(g_got, g_ref):
+        assert rel(a, r) < (1e-4 if dtype == torch.float32 else 3e-2)
+    # whole FILM module, fused linears
+    torch.manual_seed(S)
+    m = cno_model.FILM(C, dim=[2, 3], s=S)
+    with torch.no_grad():
+        for p_ in m.parameters():
+            p_.add_(0.3 * torch.randn_like(p_))
+    t = torch.rand(N)
+    xr, rr = x.float().requires_grad_(True), res.float().requires_grad_(True)
+    ym_ref = rr + m(xr, t)
+    gm_ref = torch.autograd.grad(ym_ref, [xr, rr] + list(m.parameters()), dy.float())
+    mg = copy.deepcopy(m).to(DEV)
+    xg, rg = x.to(DEV).requires_grad_(True), res.to(DEV).requires_grad_(True)
+    ym = mg(xg, t.to(DEV), residual=rg)
+    gm = torch.autograd.grad(ym, [xg, rg] + list(mg.parameters()), dy.to(DEV))
+    assert rel(ym, ym_ref) < tol
+    for a, r in zip(gm, gm_ref):
+        assert rel(a, r) < (1e-4 if dtype == torch.float32 else 4e-2)
+
+
 def test_plugin_layer_matches_reference_signatures(cno):
     """the objects get_plugin returns accept the reference's positional plugin calls."""
     P = cno.custom_ops.get_plugin

@@ -10,10 +10,11 @@ torch.backends.cudnn.allow_tf32 = False; torch.backends.cuda.matmul.allow_tf32 =
 g = np.load(os.path.join(ROOT, 'tests/golden/cno_model.npz'))
 sd = {k[3:]: torch.from_numpy(g[k]) for k in g.files if k.startswith('sd.')}
 
-def eager_film(self, x, t):
+def eager_film(self, x, t, residual=None):
     t = t.reshape(-1, 1).to(x.dtype)
     s = self.lat2scale(self.inp2lat_sacale(t)); q = self.lat2bias(self.inp2lat_bias(t))
-    return self.norm(x) * s[:, :, None, None] + q[:, :, None, None]
+    y = self.norm(x) * s[:, :, None, None] + q[:, :, None, None]
+    return y if residual is None else residual + y
 
 def run(mode, dtype=torch.float32):
     m = cno_model.CNO_time(**T.CFG).to('cuda'); m.load_state_dict(sd)
