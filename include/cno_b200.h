@@ -110,6 +110,25 @@ int cno_film_fwd_res(const void* x, const void* residual, void* y, const float* 
                      float* scale_out, float* mean, float* rstd, int dtype, int n, int c, int hw, int lat,
                      float eps, void* stream);
 
+/* CIN -> filtered_lrelu prologue fusion (CNO_timeModule_CIN.py:303-317 followed by the LReLu of the same block).
+ * cno_film_stats is cno_film_fwd without the y pass: it leaves mean, rstd, scale_out and the plane affine
+ * CIN(x)[n,c] = aff_a[n,c] * x[n,c] + aff_d[n,c]  (all fp32[N,C]).  cno_filtered_lrelu_affine is cno_filtered_lrelu on the input
+ * aff_a * x + aff_d, applied while the up-FIR runs (aff_a scales the FIR sum, aff_d joins the bias edge profile), so the normalised
+ * tensor is never written or read.  Forward modes (SIGN_WRITE / SIGN_NONE) only; aff_a = aff_d = NULL is cno_filtered_lrelu.
+ * Backward: the unchanged SIGN_READ launch gives d(CIN output), cno_cin_bwd + cno_film_bwd_finish take it from there. */
+int cno_film_stats(const void* x, const float* t, const float* gamma, const float* beta,
+                   const float* w1s, const float* b1s, const float* W2s, const float* b2s,
+                   const float* w1b, const float* b1b, const float* W2b, const float* b2b,
+                   float* scale_out, float* mean, float* rstd, float* aff_a, float* aff_d,
+                   int dtype, int n, int c, int hw, int lat, float eps, void* stream);
+int cno_filtered_lrelu_affine(const void* x, void* y, const void* b, uint8_t* mask, float* db,
+                              const float* fu, const float* fd, int dtype,
+                              int n, int c, int in_h, int in_w, int out_h, int out_w,
+                              int fu_taps, int fd_taps, int up, int down, int px0, int py0,
+                              int mask_h, int mask_w, int mask_pitch, int sx, int sy, int sign_mode,
+                              float gain, float slope, float clamp, int flip,
+                              const float* aff_a, const float* aff_d, void* stream);
+
 /* every parameter gradient of one FILM module from the per-plane sums s1, s2 of cno_cin_bwd, in one launch
  * (replaces autograd through 4 Linear layers, ~20 small kernels): dgamma, dbeta [C]; d lat2scale.weight [C,lat] / bias [C];
  * d inp2lat_sacale.weight / bias [lat]; the same four for the shift branch.  Deterministic (no atomics). */

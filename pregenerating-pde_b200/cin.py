@@ -5,12 +5,14 @@ one kernel pass (csrc/cin.cu), with a fused backward.  `film_forward` is a drop-
 that keeps the module's parameters / state_dict untouched; the four tiny Linear layers stay in torch
 (autograd carries dscale / dshift into them)."""
 import ctypes
+import os
 import torch
 
 from . import _lib
 from .torch_utils.custom_ops import _DT, _ptr, _stream
 
 
+FUSE_LRELU = os.environ.get('CNO_FUSE_LRELU', '1') != '0'         # False: film_lrelu runs FILM and the activation as two ops (the normalised tensor goes through HBM)
 FUSE_LINEARS = True       # False: keep the four Linear layers in torch (autograd supports higher-order gradients there)
 
 
@@ -80,11 +82,7 @@ class _Film(torch.autograd.Function):
         n, c, h, w = x.shape
         x = x.contiguous()
         res = None if res is None else res.to(x.dtype).contiguous()
-        f32 = lambda v: v.detach().float().contiguous()
-        t32 = f32(t).reshape(-1)
-        P = [f32(v) for v in (gamma, beta, w1s.reshape(-1), b1s, W2s, b2s, w1b.reshape(-1), b1b, W2b, b2b)]
-        lat = P[2].numel()
-        assert t32.numel() == n and P[4].shape == (c, lat) and P[8].shape == (c, lat)
+        t32, P, lat = _film_params(t, gamma, beta, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b, n, c)
         y = torch.empty_like(x)
         mean = torch.empty([n, c], dtype=torch.float32, device=x.device)
         rstd, scale = torch.empty_like(mean), torch.empty_like(mean)
@@ -99,29 +97,94 @@ class _Film(torch.autograd.Function):
     @staticmethod
     @torch.autograd.function.once_differentiable
     def backward(ctx, dy):
-        lib = _lib.load()
-        x, t32, scale, mean, rstd, gamma, beta, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b = ctx.saved_tensors
-        n, c, h, w = x.shape
-        lat = w1s.numel()
         dy = dy.contiguous()
-        dx = torch.empty_like(x)
-        s12 = torch.empty([2, n, c], dtype=torch.float32, device=x.device)
-        with torch.cuda.device(x.device):
-            rc = lib.cno_cin_bwd(_ptr(x), _ptr(dy), _ptr(dx), _ptr(gamma), _ptr(scale), _ptr(mean), _ptr(rstd), _ptr(s12[0]), _ptr(s12[1]),
-                                 _DT[x.dtype], n, c, h * w, _stream(x))
-            _lib.check(rc, 'cin_bwd')
-            # one flat buffer for the ten parameter gradients
-            sizes = [c, c, lat, lat, c * lat, c, lat, lat, c * lat, c]      # dgamma dbeta dw1s db1s dW2s db2s dw1b db1b dW2b db2b
-            flat = torch.empty([sum(sizes)], dtype=torch.float32, device=x.device)
-            g = list(flat.split(sizes))
-            rc = lib.cno_film_bwd_finish(_ptr(s12[0]), _ptr(s12[1]), _ptr(t32), _ptr(gamma), _ptr(beta), _ptr(scale),
-                                         _ptr(w1s), _ptr(b1s), _ptr(W2s), _ptr(w1b), _ptr(b1b), _ptr(W2b),
-                                         _ptr(g[0]), _ptr(g[1]), _ptr(g[4]), _ptr(g[5]), _ptr(g[2]), _ptr(g[3]),
-                                         _ptr(g[8]), _ptr(g[9]), _ptr(g[6]), _ptr(g[7]), n, c, lat, _stream(x))
-            _lib.check(rc, 'film_bwd_finish')
-        outs = [gi.view(shape).to(dt) for gi, (dt, shape) in zip(g, ctx.meta)]
+        dx, outs = _film_backward(ctx.saved_tensors, dy, ctx.meta)
         outs = [o if need else None for o, need in zip(outs, ctx.needs_input_grad[2:12])]
         return (dx if ctx.needs_input_grad[0] else None, None, *outs, None, dy if ctx.needs_input_grad[13] else None)
+
+
+def _film_params(t, gamma, beta, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b, n, c):
+    f32 = lambda v: v.detach().float().contiguous()
+    t32 = f32(t).reshape(-1)
+    P = [f32(v) for v in (gamma, beta, w1s.reshape(-1), b1s, W2s, b2s, w1b.reshape(-1), b1b, W2b, b2b)]
+    lat = P[2].numel()
+    assert t32.numel() == n and P[4].shape == (c, lat) and P[8].shape == (c, lat)
+    return t32, P, lat
+
+
+def _film_backward(saved, dy, meta):
+    """dx and the ten parameter gradients of one FILM module from (x, t, scale, mean, rstd, weights) and d(FILM output):
+    cno_cin_bwd + cno_film_bwd_finish."""
+    lib = _lib.load()
+    x, t32, scale, mean, rstd, gamma, beta, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b = saved
+    n, c, h, w = x.shape
+    lat = w1s.numel()
+    dx = torch.empty_like(x)
+    s12 = torch.empty([2, n, c], dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        rc = lib.cno_cin_bwd(_ptr(x), _ptr(dy), _ptr(dx), _ptr(gamma), _ptr(scale), _ptr(mean), _ptr(rstd), _ptr(s12[0]), _ptr(s12[1]),
+                             _DT[x.dtype], n, c, h * w, _stream(x))
+        _lib.check(rc, 'cin_bwd')
+        # one flat buffer for the ten parameter gradients
+        sizes = [c, c, lat, lat, c * lat, c, lat, lat, c * lat, c]      # dgamma dbeta dw1s db1s dW2s db2s dw1b db1b dW2b db2b
+        flat = torch.empty([sum(sizes)], dtype=torch.float32, device=x.device)
+        g = list(flat.split(sizes))
+        rc = lib.cno_film_bwd_finish(_ptr(s12[0]), _ptr(s12[1]), _ptr(t32), _ptr(gamma), _ptr(beta), _ptr(scale),
+                                     _ptr(w1s), _ptr(b1s), _ptr(W2s), _ptr(w1b), _ptr(b1b), _ptr(W2b),
+                                     _ptr(g[0]), _ptr(g[1]), _ptr(g[4]), _ptr(g[5]), _ptr(g[2]), _ptr(g[3]),
+                                     _ptr(g[8]), _ptr(g[9]), _ptr(g[6]), _ptr(g[7]), n, c, lat, _stream(x))
+        _lib.check(rc, 'film_bwd_finish')
+    return dx, [gi.view(shape).to(dt) for gi, (dt, shape) in zip(g, meta)]
+
+
+class _FilmLRelu(torch.autograd.Function):
+    """filtered_lrelu(FILM(x, t)) with the normalised tensor never written: cno_film_stats leaves the plane affine,
+    cno_filtered_lrelu_affine applies it while the up-FIR runs.  Backward: the usual SIGN_READ launch on dy gives d(FILM output) and
+    the LReLu bias gradient, then the FILM backward as in _Film.  cfg as in _FilteredLRelu (clamp = none)."""
+
+    @staticmethod
+    def forward(ctx, x, t, gamma, beta, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b, eps, fu, fd, b, cfg):
+        from .torch_utils.ops import filtered_lrelu as flr
+        lib = _lib.load()
+        flr._init()
+        n, c, h, w = x.shape
+        x = x.contiguous()
+        t32, P, lat = _film_params(t, gamma, beta, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b, n, c)
+        mean = torch.empty([n, c], dtype=torch.float32, device=x.device)
+        rstd, scale, aff_a, aff_d = (torch.empty_like(mean) for _ in range(4))
+        with torch.cuda.device(x.device):
+            rc = lib.cno_film_stats(_ptr(x), _ptr(t32), *[_ptr(v) for v in P], _ptr(scale), _ptr(mean), _ptr(rstd), _ptr(aff_a), _ptr(aff_d),
+                                    _DT[x.dtype], n, c, h * w, lat, float(eps), _stream(x))
+        _lib.check(rc, 'film_stats')
+        up, down, px0, px1, py0, py1, gain, slope, clamp, flip = cfg
+        write_signs = any(ctx.needs_input_grad)
+        y, so, rc = flr._plugin.filtered_lrelu(x, fu, fd, b.to(x.dtype), torch.empty([0]), up, down, px0, px1, py0, py1, 0, 0, gain, slope,
+                                               clamp, flip, write_signs, affine=(aff_a, aff_d))
+        if rc < 0:
+            raise RuntimeError('film_lrelu: configuration has no fused kernel (check film_lrelu_fusable first)')
+        ctx.save_for_backward(x, t32, scale, mean, rstd, *P, fu, fd, so)
+        ctx.meta = [(v.dtype, v.shape) for v in (gamma, beta, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b)]
+        ctx.cfg, ctx.y_shape, ctx.b_dtype = cfg, y.shape, b.dtype
+        return y
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, dy):
+        from .torch_utils.ops import filtered_lrelu as flr
+        *film_saved, fu, fd, si = ctx.saved_tensors
+        up, down, px0, px1, py0, py1, gain, slope, clamp, flip = ctx.cfg
+        _, _, xh, xw = film_saved[0].shape
+        _, _, yh, yw = ctx.y_shape
+        # swapped-op recipe of filtered_lrelu.py:244-256, as in _FilteredLRelu.backward
+        pp = ((fu.shape[-1] - 1) + (fd.shape[-1] - 1) - px0, xw * up - yw * down + px0 - (up - 1),
+              (fu.shape[0] - 1) + (fd.shape[0] - 1) - py0, xh * up - yh * down + py0 - (up - 1))
+        bcfg = (down, up) + pp + (gain * (up ** 2) / (down ** 2), slope, float('inf'), not flip)
+        bsx, bsy = -(fu.shape[-1] - 1) + px0, -(fu.shape[0] - 1) + py0
+        dz, _, _, _, db = flr._FilteredLRelu._run(dy.contiguous(), fd, fu, None, si, bsx, bsy, bcfg, False, want_db=True, signs_only=True)
+        dx, outs = _film_backward(film_saved, dz, ctx.meta)
+        outs = [o if need else None for o, need in zip(outs, ctx.needs_input_grad[2:12])]
+        return (dx if ctx.needs_input_grad[0] else None, None, *outs, None, None, None,
+                db.to(ctx.b_dtype) if ctx.needs_input_grad[15] else None, None)
 
 
 def _film_fusable(self, x):
@@ -151,3 +214,51 @@ def film_forward(self, x, timestep, residual=None):
     x = norm(x)
     y = x * scale.unsqueeze(2).unsqueeze(3) + shift.unsqueeze(2).unsqueeze(3)
     return y if residual is None else residual + y
+
+
+def _film_kernel_ok(self, x, timestep):
+    norm = self.norm
+    return (x.is_cuda and x.ndim == 4 and isinstance(norm, torch.nn.InstanceNorm2d) and norm.affine
+            and not norm.track_running_stats and x.dtype in _DT and x.dtype != torch.float64
+            and FUSE_LINEARS and _film_fusable(self, x) and not timestep.requires_grad)
+
+
+def film_lrelu(film, act, x, timestep):
+    """act(film(x, timestep)) for a FILM module followed by an LReLu module (CNOBlock.forward, CNO_timeModule_CIN.py:329-335;
+    ResidualBlock.forward :499-500).  When both have a fused kernel the normalised tensor is never written: one statistics pass
+    over x, then the filtered_lrelu kernel applies the plane affine in its prologue.  Anything else runs the two modules."""
+    fu, fd = getattr(act, 'up_filter', None), getattr(act, 'down_filter', None)
+    ok = (FUSE_LRELU and x.numel() > 0 and type(film).forward is film_forward and _film_kernel_ok(film, x, timestep) and getattr(act, 'impl', 'cuda') == 'cuda'
+          and isinstance(fu, torch.Tensor) and isinstance(fd, torch.Tensor) and fu.ndim == 1 and fd.ndim == 1
+          and fu.dtype == torch.float32 and fd.dtype == torch.float32 and type(act).forward is _lrelu_forward_of(act))
+    if ok:
+        up, down = int(act.up_factor), int(act.down_factor)
+        px0, px1, py0, py1 = [int(v) for v in act.padding]
+        n, c, xh, xw = x.shape
+        fut, fdt = fu.shape[0] - 1, fd.shape[0] - 1
+        cw, ch = xw * up + px0 + px1 - fut, xh * up + py0 + py1 - fut
+        ok = cw > fdt and ch > fdt
+        if ok:
+            yw, yh = (cw - fdt + down - 1) // down, (ch - fdt + down - 1) // down
+            ok = _lib.load().cno_filtered_lrelu_query(_DT[x.dtype], xh, xw, yh, yw, fu.shape[0], fd.shape[0], up, down, px0, py0) == 0
+    if not ok:
+        return act(film(x, timestep))
+    norm = film.norm
+    cfg = (up, down, px0, px1, py0, py1, float(2.0 ** 0.5), 0.2, float('inf'), False)
+    return _FilmLRelu.apply(x, timestep, norm.weight, norm.bias, film.inp2lat_sacale.weight, film.inp2lat_sacale.bias,
+                            film.lat2scale.weight, film.lat2scale.bias, film.inp2lat_bias.weight, film.inp2lat_bias.bias,
+                            film.lat2bias.weight, film.lat2bias.bias, norm.eps, fu, fd, act.bias, cfg)
+
+
+_LRELU_FORWARDS = {}
+
+
+def register_lrelu(cls):
+    """Declare that cls.forward(x) is exactly filtered_lrelu(x, fu=up_filter, fd=down_filter, b=bias, up=up_factor, down=down_factor,
+    padding=padding, gain=sqrt(2), slope=0.2, clamp=None) (training/filtered_networks.py:267-276) so film_lrelu may replace it."""
+    _LRELU_FORWARDS[cls] = cls.forward
+    return cls
+
+
+def _lrelu_forward_of(act):
+    return _LRELU_FORWARDS.get(type(act))

@@ -22,6 +22,7 @@ from .torch_utils.ops import filtered_lrelu
 from . import cin as _cin
 
 
+@_cin.register_lrelu
 class LReLu(nn.Module):
     """Alias-free activation: up-FIR -> leaky ReLU -> down-FIR (filtered_networks.py:199-278)."""
 
@@ -116,7 +117,7 @@ class CNOBlock(nn.Module):
     def forward(self, x, time):
         x = self.convolution(x)
         if self.is_time:
-            x = self.in_norm_conditiner(x, time)
+            return _cin.film_lrelu(self.in_norm_conditiner, self.activation, x, time)     # CIN folded into the activation's prologue
         return self.activation(x)
 
 
@@ -154,8 +155,9 @@ class ResidualBlock(nn.Module):
     def forward(self, x, time):
         out = self.convolution1(x)
         if self.is_time:
-            out = self.in_norm_conditiner1(out, time)
-        out = self.convolution2(self.activation(out))
+            out = self.convolution2(_cin.film_lrelu(self.in_norm_conditiner1, self.activation, out, time))
+        else:
+            out = self.convolution2(self.activation(out))
         if self.is_time:
             return self.in_norm_conditiner2(out, time, residual=x)      # x + CIN(out) in the CIN kernel's single pass
         return x + out

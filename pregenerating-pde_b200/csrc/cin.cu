@@ -99,6 +99,8 @@ struct CinParams {
     const void* res;                         // forward only, optional: y = res + CIN(x)  (ResidualBlock epilogue, CNO_timeModule_CIN.py:503-507)
     const float *gamma, *beta, *scale, *shift;
     float *mean, *rstd, *s1, *s2;
+    float *aff_a, *aff_d;                    // forward only, optional: the plane's affine y = aff_a * x + aff_d; with y == nullptr the kernel
+                                             // stops there (the consumer applies it: filtered_lrelu prologue)
     int64_t planes; int c, hw, gs; float eps;
     FilmW film;                              // film.t != nullptr: scale / shift come from the FiLM weights
 };
@@ -151,12 +153,12 @@ __global__ void __launch_bounds__(1024) cin_fwd_reg_kernel(CinParams p) {
     const int ch = (int)(plane % p.c);
     const float a = p.gamma[ch] * s * r;
     const float d0 = p.beta[ch] * s + q - mu * a;
-    if (t == 0) { p.mean[plane] = mu; p.rstd[plane] = r; }
+    if (t == 0) { p.mean[plane] = mu; p.rstd[plane] = r; if (p.aff_a) { p.aff_a[plane] = a; p.aff_d[plane] = d0; } }
     T* yp = (T*)p.y + plane * (int64_t)p.hw;
 #pragma unroll
     for (int k = 0; k < VPT; k++) {
         const int i = t + k * gs;
-        if (i < nvec) {
+        if (p.y && i < nvec) {
             float f[V]; Pack<T>::get(v[k], f);
 #pragma unroll
             for (int e = 0; e < V; e++) f[e] = fmaf(f[e], a, d0);
@@ -307,12 +309,12 @@ __global__ void __launch_bounds__(CLUSTER_CTA, 2) cin_fwd_cluster_kernel(CinPara
     const int ch = (int)(plane % p.c);
     const float a = p.gamma[ch] * s * r;
     const float d0 = p.beta[ch] * s + q - mu * a;
-    if (t == 0) { p.mean[plane] = mu; p.rstd[plane] = r; }
+    if (t == 0) { p.mean[plane] = mu; p.rstd[plane] = r; if (p.aff_a) { p.aff_a[plane] = a; p.aff_d[plane] = d0; } }
     T* yp = (T*)p.y + plane * (int64_t)p.hw;
 #pragma unroll
     for (int k = 0; k < VPT; k++) {
         const int i = t + k * gs;
-        if (i < nvec) {
+        if (p.y && i < nvec) {
             float f[V]; Pack<T>::get(v[k], f);
 #pragma unroll
             for (int e = 0; e < V; e++) f[e] = fmaf(f[e], a, d0);
@@ -394,10 +396,10 @@ __global__ void __launch_bounds__(CTA) cin_stream_kernel(CinParams p) {
         if (p.film.t) film_affine(p, true, plane, threadIdx.x, CTA, red, s, q);
         else { s = p.scale[plane]; q = p.shift[plane]; }
         const float a = p.gamma[ch] * s * r, d0 = p.beta[ch] * s + q - mu * a;
-        if (threadIdx.x == 0) { p.mean[plane] = mu; p.rstd[plane] = r; }
+        if (threadIdx.x == 0) { p.mean[plane] = mu; p.rstd[plane] = r; if (p.aff_a) { p.aff_a[plane] = a; p.aff_d[plane] = d0; } }
         T* yp = (T*)p.y + base;
         const T* rp = p.res ? (const T*)p.res + base : nullptr;
-        for (int i = threadIdx.x; i < p.hw; i += CTA) yp[i] = from_f32<T>(fmaf(to_f32(xp[i]), a, d0) + (rp ? to_f32(rp[i]) : 0.f));
+        if (p.y) for (int i = threadIdx.x; i < p.hw; i += CTA) yp[i] = from_f32<T>(fmaf(to_f32(xp[i]), a, d0) + (rp ? to_f32(rp[i]) : 0.f));
     } else {
         const T* gp = (const T*)p.dy + base;
         const float mu = p.mean[plane], r = p.rstd[plane];
@@ -618,6 +620,23 @@ extern "C" int cno_film_fwd_res(const void* x, const void* residual, void* y, co
     CNO_CHECK_ARG(n >= 0 && c > 0 && hw > 0 && lat > 0, "film_fwd: bad sizes n=%d c=%d hw=%d lat=%d", n, c, hw, lat);
     if (n == 0) return 0;
     CinParams p{}; p.x = x; p.y = y; p.res = residual; p.gamma = gamma; p.beta = beta; p.mean = mean; p.rstd = rstd;
+    p.planes = (int64_t)n * c; p.c = c; p.hw = hw; p.eps = eps;
+    p.film = FilmW{t, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b, scale_out, lat};
+    return cin_dispatch<false>(p, dtype, (cudaStream_t)stream);
+}
+
+// Statistics-only FiLM forward: per-plane mean / rstd / scale and the folded affine (aff_a, aff_d) with CIN(x) = aff_a * x + aff_d,
+// no y written.  cno_filtered_lrelu_affine consumes the pair, so the normalised tensor never exists in HBM.
+extern "C" int cno_film_stats(const void* x, const float* t, const float* gamma, const float* beta,
+                              const float* w1s, const float* b1s, const float* W2s, const float* b2s,
+                              const float* w1b, const float* b1b, const float* W2b, const float* b2b,
+                              float* scale_out, float* mean, float* rstd, float* aff_a, float* aff_d,
+                              int dtype, int n, int c, int hw, int lat, float eps, void* stream) {
+    CNO_CHECK_ARG(x && t && gamma && beta && w1s && b1s && W2s && b2s && w1b && b1b && W2b && b2b && mean && rstd && aff_a && aff_d,
+                  "film_stats: null pointer");
+    CNO_CHECK_ARG(n >= 0 && c > 0 && hw > 0 && lat > 0, "film_stats: bad sizes n=%d c=%d hw=%d lat=%d", n, c, hw, lat);
+    if (n == 0) return 0;
+    CinParams p{}; p.x = x; p.gamma = gamma; p.beta = beta; p.mean = mean; p.rstd = rstd; p.aff_a = aff_a; p.aff_d = aff_d;
     p.planes = (int64_t)n * c; p.c = c; p.hw = hw; p.eps = eps;
     p.film = FilmW{t, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b, scale_out, lat};
     return cin_dispatch<false>(p, dtype, (cudaStream_t)stream);

@@ -109,6 +109,8 @@ struct Params {
     alignas(16) float vy[4][8];      // v-up taps  [phase][k], scaled by UP * gain
     alignas(16) float fd[32];        // down taps in correlation order
     void* y; const void* b; uint8_t* mask; float* db;
+    const float* pa; const float* pd;   // AFF variants: per-plane affine applied to x before the bias: input = pa[plane] * x + pd[plane]
+                                        // (the CIN output); nullptr otherwise
     int NC, C, H, W, UH, UW, OH, OW;
     int G, P;                  // column groups per plane (ceil(UW/4)); planes per CTA
     int ncta, rows_total;      // persistent CTAs; rows_total = plane groups * OH ("global row space", see cta_rows)
@@ -187,11 +189,12 @@ template <class C> FLR_DEV int dpos(const Params& p, int f4idx) { return f4idx /
 // ------------------------------------------------------------------------------------------------
 // per-thread state of the streaming phase (lives in registers on the device)
 // ------------------------------------------------------------------------------------------------
-template <class T, class C, int MODE>
+template <class T, class C, int MODE, bool AFF = false>
 struct Stream {
     f2 win[C::WLY][2];      // h-up rows: window of the vertical up-FIR, two column pairs
     f2 acc[C::ND][2];       // rotating output-row accumulators of the vertical down-FIR
     f2 bE[2];               // bias times the horizontal edge profile of the up-FIR
+    f2 aff2;                // AFF: (a, a) of this thread's plane
     int unit, g;            // plane slot in the CTA, column group
     int dofs;               // float offset of this thread's float4 inside a D row
     bool active;
@@ -213,7 +216,7 @@ struct Stream {
         FLR_UNROLL for (int w = 0; w < C::WLY; w++) { win[w][0] = mk2(0.f, 0.f); win[w][1] = mk2(0.f, 0.f); }
         bE[0] = bE[1] = mk2(0.f, 0.f);
         colmask = 0; rd_word = 0; rd_bits = 0; mrow0 = nullptr;
-        dbw[0] = dbw[1] = dbacc[0] = dbacc[1] = mk2(0.f, 0.f); db_lo = db_hi = 0;
+        dbw[0] = dbw[1] = dbacc[0] = dbacc[1] = mk2(0.f, 0.f); db_lo = db_hi = 0; aff2 = mk2(1.f, 1.f);
         if (!active) return;
         if (FLR_IS_READ(MODE) && p.db) {       // db is a backward quantity: only the mask-reading variant carries the code
             float w[4];
@@ -226,7 +229,10 @@ struct Stream {
             dbw[0] = mk2(w[0], w[1]); dbw[1] = mk2(w[2], w[3]);
         }
         // bias edge profile: A = hup(x) + b * sum_k [column valid] * tap
-        const float bias = p.b ? ld_bias(plane % p.C) : 0.f;
+        // a constant c added before the zero padding contributes c * (sum of in-bounds taps); the affine offset d joins the bias,
+        // the affine scale a multiplies the FIR sum (hup)
+        const float bias = (p.b ? ld_bias(plane % p.C) : 0.f) + (AFF ? p.pd[plane] : 0.f);
+        if (AFF) { const float a_pl = p.pa[plane]; aff2 = mk2(a_pl, a_pl); }
         FLR_UNROLL for (int pr = 0; pr < 2; pr++) {
             const int qx = (C::UP == 2) ? 2 * g + pr : g;
             const int hp = (C::UP == 2) ? 0 : pr;
@@ -266,12 +272,13 @@ struct Stream {
 #endif
         { FLR_UNROLL for (int w = 0; w < C::NXS; w++) xs[w] = Cvt<T>::get(xrow[xoff + w]); }
         FLR_UNROLL for (int pr = 0; pr < 2; pr++) {
-            f2 a = rowvalid ? bE[pr] : mk2(0.f, 0.f);
+            const f2 edge = rowvalid ? bE[pr] : mk2(0.f, 0.f);
+            f2 a = AFF ? mk2(0.f, 0.f) : edge;
             const int qo = (C::UP == 2) ? pr : 0;
             const int hp = (C::UP == 2) ? 0 : pr;
             FLR_UNROLL for (int k = 0; k < C::WLX; k++)
                 a = ffma2(mk2(xs[qo + k], xs[qo + k]), mk2(p.hx[hp][k][0], p.hx[hp][k][1]), a);
-            out[pr] = a;
+            out[pr] = AFF ? ffma2(a, aff2, edge) : a;
         }
     }
 

@@ -21,12 +21,33 @@ extern "C" int cno_filtered_lrelu_query(int dtype, int in_h, int in_w, int out_h
                      px0, py0, 1.f, 0.f, -1.f, 0, 0);
 }
 
+extern "C" int cno_filtered_lrelu_affine(const void* x, void* y, const void* b, uint8_t* mask, float* db,
+                                         const float* fu, const float* fd, int dtype,
+                                         int n, int c, int in_h, int in_w, int out_h, int out_w,
+                                         int fu_taps, int fd_taps, int up, int down, int px0, int py0,
+                                         int mask_h, int mask_w, int mask_pitch, int sx, int sy, int sign_mode,
+                                         float gain, float slope, float clamp, int flip,
+                                         const float* aff_a, const float* aff_d, void* stream);
+
 extern "C" int cno_filtered_lrelu(const void* x, void* y, const void* b, uint8_t* mask, float* db,
                                   const float* fu, const float* fd, int dtype,
                                   int n, int c, int in_h, int in_w, int out_h, int out_w,
                                   int fu_taps, int fd_taps, int up, int down, int px0, int py0,
                                   int mask_h, int mask_w, int mask_pitch, int sx, int sy, int sign_mode,
                                   float gain, float slope, float clamp, int flip, void* stream) {
+    return cno_filtered_lrelu_affine(x, y, b, mask, db, fu, fd, dtype, n, c, in_h, in_w, out_h, out_w, fu_taps, fd_taps, up, down,
+                                     px0, py0, mask_h, mask_w, mask_pitch, sx, sy, sign_mode, gain, slope, clamp, flip,
+                                     nullptr, nullptr, stream);
+}
+
+extern "C" int cno_filtered_lrelu_affine(const void* x, void* y, const void* b, uint8_t* mask, float* db,
+                                         const float* fu, const float* fd, int dtype,
+                                         int n, int c, int in_h, int in_w, int out_h, int out_w,
+                                         int fu_taps, int fd_taps, int up, int down, int px0, int py0,
+                                         int mask_h, int mask_w, int mask_pitch, int sx, int sy, int sign_mode,
+                                         float gain, float slope, float clamp, int flip,
+                                         const float* aff_a, const float* aff_d, void* stream) {
+    CNO_CHECK_ARG((aff_a == nullptr) == (aff_d == nullptr), "filtered_lrelu: aff_a and aff_d go together");
     CNO_CHECK_ARG(x && y && fu && fd, "filtered_lrelu: null pointer");
     CNO_CHECK_ARG(sign_mode >= 0 && sign_mode <= 3, "filtered_lrelu: bad sign_mode %d", sign_mode);
     const bool reading = sign_mode == CNO_SIGN_READ || sign_mode == CNO_SIGN_READ_SIGNONLY;
@@ -42,7 +63,8 @@ extern "C" int cno_filtered_lrelu(const void* x, void* y, const void* b, uint8_t
     Params& p = plan.p;
     if (sign_mode == CNO_SIGN_WRITE)
         CNO_CHECK_ARG(mask_h >= p.UH && mask_pitch >= p.G, "filtered_lrelu: mask [%d rows x %d bytes] smaller than [%d x %d]", mask_h, mask_pitch, p.UH, p.G);
-    p.y = y; p.b = b; p.mask = mask; p.db = db;
+    p.y = y; p.b = b; p.mask = mask; p.db = db; p.pa = aff_a; p.pd = aff_d;
+    if (aff_a && (sign_mode == CNO_SIGN_READ || sign_mode == CNO_SIGN_READ_SIGNONLY)) return -1;   // the affine belongs to the forward
     if (reading) {
         if (((uintptr_t)mask & 3u) || (mask_pitch & 3)) return -1;     // staged with aligned 32-bit copies
         set_mask_window(plan, sx);

@@ -64,7 +64,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 //                the h-down of body k-1 runs AFTER body k, so its wait on full[k-1] has had a whole body to complete, and the
 //                wait in front of body k+1 (guard for reusing D[(k+1) % 3] and the x slot / mask buffer of body k) comes after
 //                that h-down work.  Warps therefore drift by up to one h-down phase without stalling each other.
-template <class T, class C, int MODE>
+template <class T, class C, int MODE, bool AFF>
 __global__ void __launch_bounds__(FLR_MAXT, FLR_MINB)
 flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ Params p) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -119,7 +119,7 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         };
         if (tid == 0) while (next_load < cg.nstages_total && next_load < NSTAGE) issue(next_load++);
 
-        Stream<T, C, MODE> st;
+        Stream<T, C, MODE, AFF> st;
         st.init(p, cg, tid, [&](int ch) { return Cvt<T>::get(reinterpret_cast<const T*>(p.b)[ch]); });
 
         if (FLR_IS_READ(MODE)) stage_mask<C>(p, cg, cg.j_b0, tid, blockDim.x, M, copy4);
@@ -201,9 +201,9 @@ inline int env_ctas() {
     return v;
 }
 
-template <class T, class C, int MODE>
+template <class T, class C, int MODE, bool AFF = false>
 int launch_variant(const Plan& plan, const CUtensorMap& map, cudaStream_t st) {
-    auto kern = flr_fused_kernel<T, C, MODE>;
+    auto kern = flr_fused_kernel<T, C, MODE, AFF>;
     static size_t configured = 0;      // per instantiation
     if (plan.smem_bytes > configured) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem_bytes);
@@ -228,6 +228,11 @@ int launch_variant(const Plan& plan, const CUtensorMap& map, cudaStream_t st) {
 
 template <class T, class C>
 int launch_mode(const Plan& plan, const CUtensorMap& map, int mode, cudaStream_t st) {
+    if (plan.p.pa) {                      // CIN affine folded into the x load: forward variants only
+        if (mode == CNO_SIGN_WRITE) return launch_variant<T, C, SIGN_WRITE, true>(plan, map, st);
+        if (mode == CNO_SIGN_NONE) return launch_variant<T, C, SIGN_NONE, true>(plan, map, st);
+        return -1;
+    }
     if (mode == CNO_SIGN_WRITE) return launch_variant<T, C, SIGN_WRITE>(plan, map, st);
     if (mode == CNO_SIGN_READ) return launch_variant<T, C, SIGN_READ>(plan, map, st);
     if (mode == CNO_SIGN_READ_SIGNONLY) return launch_variant<T, C, SIGN_READ_SO>(plan, map, st);

@@ -36,6 +36,12 @@ def patch_reference(cno_root=None, patch_film=True):
             if 'film_forward' not in _saved:
                 _saved['film_forward'] = film_mod.FILM.forward
             film_mod.FILM.forward = _cin.film_forward
+            if hasattr(film_mod, 'LReLu'):
+                _cin.register_lrelu(film_mod.LReLu)      # training/filtered_networks.py:267-276 is the call film_lrelu replaces
+            if hasattr(film_mod, 'CNOBlock'):
+                if 'cno_block_forward' not in _saved:
+                    _saved['cno_block_forward'] = film_mod.CNOBlock.forward
+                film_mod.CNOBlock.forward = _cno_block_forward
             if hasattr(film_mod, 'ResidualBlock'):
                 if 'residual_forward' not in _saved:
                     _saved['residual_forward'] = film_mod.ResidualBlock.forward
@@ -43,14 +49,22 @@ def patch_reference(cno_root=None, patch_film=True):
     return True
 
 
+def _cno_block_forward(self, x, time):
+    """CNOBlock.forward (CNO_timeModule_CIN.py:329-335) with the CIN folded into the activation's prologue (cin.film_lrelu)."""
+    timed = self.is_time == 1 or self.is_time is True
+    if not (timed and isinstance(self.batch_norm, torch.nn.Identity)):
+        return _saved['cno_block_forward'](self, x, time)
+    return _cin.film_lrelu(self.in_norm_conditiner, self.activation, self.convolution(x), time)
+
+
 def _residual_forward(self, x, time):
-    """ResidualBlock.forward (CNO_timeModule_CIN.py:496-510) with the closing `x + out` folded into the second CIN's kernel.
+    """ResidualBlock.forward (CNO_timeModule_CIN.py:496-510) with the first CIN folded into the activation's prologue and the closing
+    `x + out` folded into the second CIN's kernel.
     Any flavour other than time conditioning with Identity batch norms runs the reference's own forward."""
     timed = self.is_time == 1 or self.is_time is True
     if not (timed and isinstance(self.batch_norm1, torch.nn.Identity) and isinstance(self.batch_norm2, torch.nn.Identity)):
         return _saved['residual_forward'](self, x, time)
-    out = self.in_norm_conditiner1(self.convolution1(x), time)
-    out = self.convolution2(self.activation(out))
+    out = self.convolution2(_cin.film_lrelu(self.in_norm_conditiner1, self.activation, self.convolution1(x), time))
     return self.in_norm_conditiner2(out, time, residual=x)
 
 
@@ -61,5 +75,7 @@ def unpatch_reference():
             importlib.import_module(f'torch_utils.ops.{name}')._plugin = None
     if 'film_forward' in _saved:
         importlib.import_module('CNO_timeModule_CIN').FILM.forward = _saved.pop('film_forward')
+    if 'cno_block_forward' in _saved:
+        importlib.import_module('CNO_timeModule_CIN').CNOBlock.forward = _saved.pop('cno_block_forward')
     if 'residual_forward' in _saved:
         importlib.import_module('CNO_timeModule_CIN').ResidualBlock.forward = _saved.pop('residual_forward')

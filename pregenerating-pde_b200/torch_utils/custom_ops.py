@@ -134,11 +134,19 @@ def _upfirdn2d_call(x, f, separable, upx, upy, downx, downy, padx0, padx1, pady0
 class _FilteredLReluPlugin:
     @staticmethod
     def filtered_lrelu(x, fu, fd, b, si, up, down, px0, px1, py0, py1, sx, sy, gain, slope, clamp, flip_filter, write_signs,
-                       db=None, signs_only=False):
+                       db=None, signs_only=False, affine=None):
         """filtered_lrelu.cpp:8-201 -> (y, so, return_code); return_code -1 = use the generic composition.
         db (extension, optional): zeroed fp32 [C] tensor that receives y.sum([0,2,3]) from the same kernel.
         signs_only (extension, optional): the caller knows `si` was written with clamp = none (no "clamped" codes), which lets
-        the kernel skip that test; the default is always correct."""
+        the kernel skip that test; the default is always correct.
+        affine (extension, optional): (a, d) fp32 [N,C] tensors; the op runs on a[n,c] * x + d[n,c] without materialising it
+        (CIN -> filtered_lrelu prologue fusion, forward calls only)."""
+        if affine is not None:
+            a_, d_ = affine
+            ok = all(v.dtype == torch.float32 and v.is_contiguous() and v.device == x.device and v.numel() == x.shape[0] * x.shape[1]
+                     for v in (a_, d_))
+            if not ok or si.numel() > 0:
+                raise RuntimeError('affine must be two contiguous float32 [N,C] tensors on the device of x, forward calls only')
         if db is not None and not (db.dtype == torch.float32 and db.is_contiguous() and db.device == x.device and db.numel() == x.shape[1]):
             raise RuntimeError('db must be a contiguous float32 [C] tensor on the device of x')
         lib = _lib.load()
@@ -196,12 +204,13 @@ class _FilteredLReluPlugin:
             mode = _lib.SIGN_READ_SIGNONLY if signs_only else _lib.SIGN_READ
         tu, td = host_taps(fu), host_taps(fd)
         with torch.cuda.device(x.device):
-            rc = lib.cno_filtered_lrelu(_ptr(x), _ptr(y), _ptr(b), _ptr(s), _ptr(db),
-                                        tu.ctypes.data_as(ctypes.c_void_p), td.ctypes.data_as(ctypes.c_void_p), dt,
-                                        n, c, xh, xw, yh, yw, fu.shape[0], fd.shape[0], up, down, px0, py0,
-                                        s.shape[2] if s is not None else 0, mask_w, s.shape[3] if s is not None else 0,
-                                        int(sx), int(sy), mode, float(gain), float(slope), -1.0, int(bool(flip_filter)),
-                                        _stream(x))
+            rc = lib.cno_filtered_lrelu_affine(_ptr(x), _ptr(y), _ptr(b), _ptr(s), _ptr(db),
+                                               tu.ctypes.data_as(ctypes.c_void_p), td.ctypes.data_as(ctypes.c_void_p), dt,
+                                               n, c, xh, xw, yh, yw, fu.shape[0], fd.shape[0], up, down, px0, py0,
+                                               s.shape[2] if s is not None else 0, mask_w, s.shape[3] if s is not None else 0,
+                                               int(sx), int(sy), mode, float(gain), float(slope), -1.0, int(bool(flip_filter)),
+                                               _ptr(affine[0]) if affine is not None else None,
+                                               _ptr(affine[1]) if affine is not None else None, _stream(x))
         if _lib.check(rc, 'filtered_lrelu') < 0:
             return none
         return y, so, 0

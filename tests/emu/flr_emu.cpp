@@ -8,7 +8,7 @@
 
 using namespace flr;
 
-template <class C, int MODE>
+template <class C, int MODE, bool AFF = false>
 static void run(const Plan& plan, const float* x, float* y, const float* bias) {
     const Params& p = plan.p;
     const int nthreads = plan.threads;
@@ -34,7 +34,7 @@ static void run(const Plan& plan, const float* x, float* y, const float* bias) {
         int gs0 = 0;
         for (int gr = r0; gr < r1;) {
             const CtaGeom cg = seg_geom<C>(p, gr, r1);
-            std::vector<Stream<float, C, MODE>> th(nthreads);
+            std::vector<Stream<float, C, MODE, AFF>> th(nthreads);
             int next_load = 0;
             auto issue = [&](int s) { tma((gs0 + s) % NSTAGE, cg.row0 + s * C::RS, cg.plane0); };
             while (next_load < cg.nstages_total && next_load < NSTAGE) issue(next_load++);
@@ -65,21 +65,39 @@ static void run(const Plan& plan, const float* x, float* y, const float* bias) {
 
 template <class C>
 static void run_mode(const Plan& plan, int mode, const float* x, float* y, const float* b) {
-    if (mode == SIGN_WRITE) run<C, SIGN_WRITE>(plan, x, y, b);
+    if (plan.p.pa && mode == SIGN_WRITE) run<C, SIGN_WRITE, true>(plan, x, y, b);
+    else if (plan.p.pa) run<C, SIGN_NONE, true>(plan, x, y, b);
+    else if (mode == SIGN_WRITE) run<C, SIGN_WRITE>(plan, x, y, b);
     else if (mode == SIGN_READ) run<C, SIGN_READ>(plan, x, y, b);
     else if (mode == SIGN_READ_SO) run<C, SIGN_READ_SO>(plan, x, y, b);
     else run<C, SIGN_NONE>(plan, x, y, b);
 }
 
+extern "C" int flr_emulate_affine(const float* x, float* y, const float* b, uint8_t* mask, int n, int c, int in_h, int in_w,
+                                  int out_h, int out_w, const float* fu, int fu_taps, const float* fd, int fd_taps, int up,
+                                  int down, int px0, int py0, int mask_h, int mask_w, int mask_pitch, int sx, int sy,
+                                  int mode, float gain, float slope, float clamp, int flip, int ctas, int* info,
+                                  const float* pa, const float* pd);
+
 extern "C" int flr_emulate(const float* x, float* y, const float* b, uint8_t* mask, int n, int c, int in_h, int in_w,
                            int out_h, int out_w, const float* fu, int fu_taps, const float* fd, int fd_taps, int up,
                            int down, int px0, int py0, int mask_h, int mask_w, int mask_pitch, int sx, int sy,
                            int mode, float gain, float slope, float clamp, int flip, int ctas, int* info) {
+    return flr_emulate_affine(x, y, b, mask, n, c, in_h, in_w, out_h, out_w, fu, fu_taps, fd, fd_taps, up, down, px0, py0, mask_h, mask_w,
+                              mask_pitch, sx, sy, mode, gain, slope, clamp, flip, ctas, info, nullptr, nullptr);
+}
+
+// the AFF variants (CIN affine folded into the x load): input = pa[plane] * x + pd[plane]
+extern "C" int flr_emulate_affine(const float* x, float* y, const float* b, uint8_t* mask, int n, int c, int in_h, int in_w,
+                                  int out_h, int out_w, const float* fu, int fu_taps, const float* fd, int fd_taps, int up,
+                                  int down, int px0, int py0, int mask_h, int mask_w, int mask_pitch, int sx, int sy,
+                                  int mode, float gain, float slope, float clamp, int flip, int ctas, int* info,
+                                  const float* pa, const float* pd) {
     Plan plan;
     if (make_plan(plan, 4, n, c, in_h, in_w, out_h, out_w, fu, fu_taps, fd, fd_taps, up, down, px0, py0, gain, slope,
                   clamp, flip, ctas) != 0) return -1;
     plan.p.b = b; plan.p.mask = mask; plan.p.mask_h = mask_h; plan.p.mask_w = mask_w; plan.p.mask_pitch = mask_pitch;
-    plan.p.sx = sx; plan.p.sy = sy;
+    plan.p.sx = sx; plan.p.sy = sy; plan.p.pa = pa; plan.p.pd = pd;
     if (mode == SIGN_READ || mode == SIGN_READ_SO) set_mask_window(plan, sx);
     if (info) { info[0] = plan.p.P; info[1] = plan.threads; info[2] = plan.blocks; info[3] = plan.p.ncta; info[4] = (int)plan.smem_bytes; }
 #define V(U, D, R) if (plan.up == U && plan.down == D && plan.rx == R && plan.ry == R) { run_mode<Cfg<U, D, R, R>>(plan, mode, x, y, b); return 0; }

@@ -27,7 +27,7 @@ def fp(a):
     return a.ctypes.data_as(ctypes.c_void_p)
 
 
-def run_emu(x, b, fu, fd, up, down, pad, gain, slope, clamp, flip, mode, mask=None, mask_geom=None, sxy=(0, 0), bands=0):
+def run_emu(x, b, fu, fd, up, down, pad, gain, slope, clamp, flip, mode, mask=None, mask_geom=None, sxy=(0, 0), bands=0, affine=None):
     n, c, h, w = x.shape
     oh, ow = O.filtered_lrelu_out_size((h, w), torch.from_numpy(fu), torch.from_numpy(fd), up, down, pad)
     y = np.full((n, c, oh, ow), np.nan, np.float32)
@@ -38,11 +38,12 @@ def run_emu(x, b, fu, fd, up, down, pad, gain, slope, clamp, flip, mode, mask=No
         mask = np.zeros((n, c, mask_geom[0], mask_geom[2]), np.uint8)
     info = (ctypes.c_int * 5)()
     bz = b if b is not None else np.zeros(c, np.float32)
-    rc = emu().flr_emulate(fp(x), fp(y), fp(bz) if b is not None else None, fp(mask), n, c, h, w, oh, ow,
-                           fp(fu), len(fu), fp(fd), len(fd), up, down, pad[0], pad[2],
-                           mask_geom[0], mask_geom[1], mask_geom[2], sxy[0], sxy[1], mode,
-                           ctypes.c_float(gain), ctypes.c_float(slope), ctypes.c_float(-1.0 if clamp is None else clamp),
-                           int(flip), bands, info)
+    pa, pd = (fp(affine[0]), fp(affine[1])) if affine is not None else (None, None)
+    rc = emu().flr_emulate_affine(fp(x), fp(y), fp(bz) if b is not None else None, fp(mask), n, c, h, w, oh, ow,
+                                  fp(fu), len(fu), fp(fd), len(fd), up, down, pad[0], pad[2],
+                                  mask_geom[0], mask_geom[1], mask_geom[2], sxy[0], sxy[1], mode,
+                                  ctypes.c_float(gain), ctypes.c_float(slope), ctypes.c_float(-1.0 if clamp is None else clamp),
+                                  int(flip), bands, info, pa, pd)
     return rc, y, mask, list(info)
 
 
@@ -141,3 +142,29 @@ def test_plan_refuses_unsupported():
     for kw in (dict(clamp=0.5, slope=0.2), dict(clamp=None, slope=1.5)):   # clamp / slope > 1 -> generic composition
         rc, *_ = run_emu(x, None, cfg['fu'].numpy(), cfg['fd'].numpy(), 2, 2, cfg['padding'], 1.0, kw['slope'], kw['clamp'], False, 0)
         assert rc == -1
+
+
+@pytest.mark.parametrize('name,s_in,s_out,N,C,bands', [CASES[0], CASES[1], CASES[2], CASES[6], CASES[12]])
+def test_emulated_affine_prologue(name, s_in, s_out, N, C, bands):
+    """AFF variants: the kernel fed x with the plane affine (a, d) equals the plain kernel math on a*x + d --
+    checked against the oracle's filtered_lrelu of the materialised tensor, outputs and sign mask."""
+    cfg = O.lrelu_config(s_in, s_out)
+    fu, fd, up, down, pad = cfg['fu'], cfg['fd'], cfg['up'], cfg['down'], cfg['padding']
+    g = torch.Generator().manual_seed(s_in * 11 + s_out)
+    x = torch.randn(N, C, s_in, s_in, generator=g) * 3 + 1
+    b = torch.randn(C, generator=g)
+    a = torch.randn(N, C, generator=g)
+    d = torch.randn(N, C, generator=g)
+    gain, slope = math.sqrt(2), 0.2
+    z = x * a[:, :, None, None] + d[:, :, None, None]
+    y_ref = O.filtered_lrelu(z, fu, fd, b, up=up, down=down, padding=pad, gain=gain, slope=slope)
+    for mode in (0, 1):
+        rc, y, mask, _ = run_emu(x.numpy(), b.numpy(), fu.numpy(), fd.numpy(), up, down, pad, gain, slope, None, False, mode, bands=bands,
+                                 affine=(a.numpy().copy(), d.numpy().copy()))
+        assert rc == 0
+        assert not np.isnan(y).any()
+        assert rel(y, y_ref.numpy()) < 2e-5          # fp32, different summation order (a * FIR(x) + d * edge vs FIR(a*x + d))
+    # the mask written by the AFF variant drives the plain backward to the gradient of the materialised composition
+    rc, _, mask0, _ = run_emu(z.numpy(), b.numpy(), fu.numpy(), fd.numpy(), up, down, pad, gain, slope, None, False, 1, bands=bands)
+    differ = np.unpackbits(mask ^ mask0).sum()
+    assert differ <= max(2, mask.size // 20000)      # sign flips only where the pre-activation is ~0 (rounding)

@@ -502,6 +502,83 @@ def test_cin_residual_epilogue(cno, N, C, S, dtype):
     assert rel(ym, ym_ref) < tol
     for a, r in zip(gm, gm_ref):
         assert rel(a, r) < (1e-4 if dtype == torch.float32 else 4e-2)
+@pytest.mark.gpu
+@pytest.mark.parametrize('s_in,s_out,N,C', [(16, 16, 2, 3), (32, 16, 3, 5), (16, 32, 2, 4), (64, 64, 2, 6), (128, 128, 2, 3), (8, 8, 32, 40)])
+def test_film_lrelu_prologue_fusion(cno, s_in, s_out, N, C, monkeypatch):
+    """LReLu(FILM(x, t)) with the CIN affine applied inside the filtered_lrelu kernel (cno_film_stats +
+    cno_filtered_lrelu_affine).  Checked against FILM in eager torch on the CPU followed by the oracle's filtered_lrelu:
+    output and every gradient (x, the ten FILM parameters, the LReLu bias); and against the two-kernel path on the GPU."""
+    from pregenerating_pde_b200 import cno_model
+    import copy
+    torch.manual_seed(s_in * 5 + s_out)
+    film = cno_model.FILM(C, dim=[2, 3], s=s_in)
+    act = cno_model.LReLu(C, C, s_in, s_out, **cno_model._filter_args(s_in, s_out, 2.0001, 0.8))
+    with torch.no_grad():
+        for p_ in list(film.parameters()) + [act.bias]:
+            p_.add_(0.3 * torch.randn_like(p_))
+    x = torch.randn(N, C, s_in, s_in) * 1.5 + 0.3
+    t = torch.rand(N)
+    xr = x.clone().requires_grad_(True)
+    z = film(xr, t)                                                # CPU tensors: the module's own torch ops
+    y_ref = O.filtered_lrelu(z, act.up_filter, act.down_filter, act.bias, up=act.up_factor, down=act.down_factor, padding=act.padding,
+                             gain=math.sqrt(2), slope=0.2)
+    dy = torch.randn_like(y_ref)
+    params = list(film.parameters()) + [act.bias]
+    g_ref = torch.autograd.grad(y_ref, [xr] + params, dy)
+
+    fg, ag = copy.deepcopy(film).to(DEV), copy.deepcopy(act).to(DEV)
+    pg = list(fg.parameters()) + [ag.bias]
+    xg = x.to(DEV).requires_grad_(True)
+    y = cno.cin.film_lrelu(fg, ag, xg, t.to(DEV))
+    assert 'FilmLRelu' in type(y.grad_fn).__name__, 'the fused path did not run'
+    g = torch.autograd.grad(y, [xg] + pg, dy.to(DEV))
+    assert rel(y, y_ref) < 3e-5
+    names = ['x'] + [n for n, _ in film.named_parameters()] + ['lrelu.bias']
+    for nm, a, r in zip(names, g, g_ref):
+        assert a.shape == r.shape and rel(a, r) < 2e-4, nm
+    # the two-kernel path (normalised tensor through HBM) on the same inputs
+    monkeypatch.setattr(cno.cin, 'FUSE_LRELU', False)
+    x2 = x.to(DEV).requires_grad_(True)
+    y2 = cno.cin.film_lrelu(fg, ag, x2, t.to(DEV))
+    assert 'FilmLRelu' not in type(y2.grad_fn).__name__
+    g2 = torch.autograd.grad(y2, [x2] + pg, dy.to(DEV))
+    assert rel(y, y2) < 3e-5
+    for nm, a, r in zip(names, g, g2):
+        assert rel(a, r) < 2e-4, nm
+    # inference: no mask is written, same values
+    monkeypatch.setattr(cno.cin, 'FUSE_LRELU', True)
+    with torch.no_grad():
+        y3 = cno.cin.film_lrelu(fg, ag, x.to(DEV), t.to(DEV))
+    assert torch.equal(y3, y)
+
+
+@pytest.mark.gpu
+def test_film_stats_c_abi(cno):
+    """cno_film_stats: mean / rstd / scale equal cno_film_fwd's, and aff_a * x + aff_d reproduces its y (same fmaf)."""
+    lib = cno._lib.load()
+    from pregenerating_pde_b200.torch_utils.custom_ops import _ptr, _stream
+    for N, C, S in [(4, 16, 32), (2, 3, 10), (1, 2, 256)]:
+        g = torch.Generator().manual_seed(S)
+        x = (torch.randn(N, C, S, S, generator=g) * 2 + 0.5).to(DEV)
+        t = torch.rand(N, generator=g).to(DEV)
+        lat = 128
+        P = [torch.randn(sz, generator=g).to(DEV) for sz in ([C], [C], [lat], [lat], [C, lat], [C], [lat], [lat], [C, lat], [C])]
+        y = torch.empty_like(x)
+        outs = [torch.empty(N, C, device=DEV) for _ in range(8)]      # scale mean rstd | scale mean rstd a d
+        rc = lib.cno_film_fwd(_ptr(x), _ptr(y), _ptr(t), *[_ptr(v) for v in P], _ptr(outs[0]), _ptr(outs[1]), _ptr(outs[2]),
+                              0, N, C, S * S, lat, 1e-5, _stream(x))
+        assert rc == 0
+        rc = lib.cno_film_stats(_ptr(x), _ptr(t), *[_ptr(v) for v in P], _ptr(outs[3]), _ptr(outs[4]), _ptr(outs[5]), _ptr(outs[6]),
+                                _ptr(outs[7]), 0, N, C, S * S, lat, 1e-5, _stream(x))
+        assert rc == 0
+        for i in range(3):
+            assert torch.equal(outs[i], outs[3 + i])
+        y2 = torch.addcmul(outs[7][:, :, None, None], x, outs[6][:, :, None, None])
+        assert rel(y2, y) < 1e-6
+    # argument errors come back as return codes with a message, not as a crash
+    assert lib.cno_film_stats(None, None, *[None] * 10, None, None, None, None, None, 0, 1, 1, 1, 1, 1e-5, None) != 0
+
+
 
 
 def test_plugin_layer_matches_reference_signatures(cno):

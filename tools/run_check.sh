@@ -6,3 +6,4 @@ python bench.py --sweep > gpurun_out/sweep.log 2>&1; tail -2 gpurun_out/sweep.lo
 cp profiles/sweep_latest.json gpurun_out/ 2>/dev/null
 python bench.py --workload cno_train --steps 10 --warmup 3 > gpurun_out/bench_train.json 2>> gpurun_out/bench.err; cut -c1-400 gpurun_out/bench_train.json
 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
+CNO_FUSE_LRELU=0 python bench.py --workload cno_train --steps 10 --warmup 3 > gpurun_out/bench_train_unfused.json 2>> gpurun_out/bench.err; cut -c1-200 gpurun_out/bench_train_unfused.json
