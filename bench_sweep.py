@@ -163,6 +163,54 @@ def sweep_cin(rows, N, C, S, dtype, reps):
     rows.append(row('cin (FILM bwd, 2 kernels)', shape, dtype, 'bwd', us_b, 3 * n * es))
 
 
+def sweep_film_lrelu(rows, N, C, S, dtype, reps):
+    """LReLu(FILM(x, t)) forward, I-config, sign mask written: the prologue-fused pair (cno_film_stats + cno_filtered_lrelu_affine,
+    no normalised tensor in HBM) beside the two-kernel form (cno_film_fwd + cno_filtered_lrelu).  Algorithmic bytes of both rows =
+    x read once + y + mask written."""
+    from pregenerating_pde_b200.torch_utils.custom_ops import _ptr, _stream, _DT
+    lib = cno._lib.load()
+    plug = cno.custom_ops.get_plugin('filtered_lrelu_plugin')
+    film = cno_model.FILM(C, dim=[2, 3], s=S).to(DEV)
+    act = cno_model.lrelu_for(C, S, S).to(DEV)
+    up, down = act.up_factor, act.down_factor
+    px0, px1, py0, py1 = act.padding
+    fu, fd = act.up_filter, act.down_filter
+    es = torch.empty(0, dtype=dtype).element_size()
+    sh = S * down - (down - 1) + (fd.numel() - 1)
+    swb = ((sh + 15) // 16 * 16) // 4
+    nbytes = N * C * (2 * S * S * es + sh * swb) + C * es
+    nrot = rot_count(nbytes + N * C * S * S * es)
+    xs = [torch.randn(N, C, S, S, device=DEV, dtype=dtype) for _ in range(nrot)]
+    zs = [torch.empty_like(x) for x in xs]
+    t = torch.rand(N, device=DEV)
+    P = [film.norm.weight, film.norm.bias, film.inp2lat_sacale.weight.reshape(-1), film.inp2lat_sacale.bias, film.lat2scale.weight,
+         film.lat2scale.bias, film.inp2lat_bias.weight.reshape(-1), film.inp2lat_bias.bias, film.lat2bias.weight, film.lat2bias.bias]
+    P = [v.detach().contiguous() for v in P]
+    lat = P[2].numel()
+    mean, rstd, scale, fa, fb = (torch.empty(N, C, device=DEV) for _ in range(5))
+    b = torch.randn(C, device=DEV, dtype=dtype)
+    e = torch.empty(0)
+    gain, slope = math.sqrt(2), 0.2
+
+    def fused(i):
+        x = xs[i % nrot]
+        rc = lib.cno_film_stats(_ptr(x), _ptr(t), *[_ptr(v) for v in P], _ptr(scale), _ptr(mean), _ptr(rstd), _ptr(fa), _ptr(fb),
+                                _DT[dtype], N, C, S * S, lat, 1e-5, _stream(t))
+        assert rc == 0
+        assert plug.filtered_lrelu(x, fu, fd, b, e, up, down, px0, px1, py0, py1, 0, 0, gain, slope, float('inf'), False, True,
+                                   affine=(fa, fb))[2] == 0
+
+    def two(i):
+        x, z = xs[i % nrot], zs[i % nrot]
+        rc = lib.cno_film_fwd(_ptr(x), _ptr(z), _ptr(t), *[_ptr(v) for v in P], _ptr(scale), _ptr(mean), _ptr(rstd),
+                              _DT[dtype], N, C, S * S, lat, 1e-5, _stream(t))
+        assert rc == 0
+        assert plug.filtered_lrelu(z, fu, fd, b, e, up, down, px0, px1, py0, py1, 0, 0, gain, slope, float('inf'), False, True)[2] == 0
+    shape = f'[{N},{C},{S},{S}] I'
+    rows.append(row('film+lrelu fwd, fused pair', shape, dtype, 'fwd', time_graph(fused, nrot, reps), nbytes))
+    rows.append(row('film+lrelu fwd, two ops', shape, dtype, 'fwd', time_graph(two, nrot, reps), nbytes))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--quick', action='store_true')
@@ -191,6 +239,8 @@ def main():
         for C, H in levels + [(64, 128)]:
             sweep_cin(rows, N, C, H, dt, reps)
         sweep_cin(rows, 8, 64, 256, dt, reps)                                 # wide fine-tune planes: thread-block cluster kernels
+        for C, H in [(64, 128), (16, 128), (64, 32)]:
+            sweep_film_lrelu(rows, N, C, H, dt, reps)                         # CIN -> filtered_lrelu prologue fusion
     out = dict(gpu=torch.cuda.get_device_name(0), hbm_peak_gbs=peak(), rows=rows)
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     json.dump(out, open(args.out, 'w'), indent=1)
