@@ -206,7 +206,16 @@ def sweep_film_lrelu(rows, N, C, S, dtype, reps):
                               _DT[dtype], N, C, S * S, lat, 1e-5, _stream(t))
         assert rc == 0
         assert plug.filtered_lrelu(z, fu, fd, b, e, up, down, px0, px1, py0, py1, 0, 0, gain, slope, float('inf'), False, True)[2] == 0
+    def stats(i):
+        assert lib.cno_film_stats(_ptr(xs[i % nrot]), _ptr(t), *[_ptr(v) for v in P], _ptr(scale), _ptr(mean), _ptr(rstd), _ptr(fa), _ptr(fb),
+                                  _DT[dtype], N, C, S * S, lat, 1e-5, _stream(t)) == 0
+
+    def flr_aff(i):
+        assert plug.filtered_lrelu(xs[i % nrot], fu, fd, b, e, up, down, px0, px1, py0, py1, 0, 0, gain, slope, float('inf'), False, True,
+                                   affine=(fa, fb))[2] == 0
     shape = f'[{N},{C},{S},{S}] I'
+    rows.append(row('film stats (read-only pass)', shape, dtype, 'fwd', time_graph(stats, nrot, reps), N * C * S * S * es))
+    rows.append(row('filtered_lrelu, affine in', shape, dtype, 'fwd', time_graph(flr_aff, nrot, reps), nbytes))
     rows.append(row('film+lrelu fwd, fused pair', shape, dtype, 'fwd', time_graph(fused, nrot, reps), nbytes))
     rows.append(row('film+lrelu fwd, two ops', shape, dtype, 'fwd', time_graph(two, nrot, reps), nbytes))
 
