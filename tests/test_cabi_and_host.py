@@ -131,6 +131,34 @@ def test_film_forward_cpu_path_equals_module(pkg, golden):
     assert torch.allclose(y, torch.from_numpy(g[f'{name}.y']), atol=1e-5)
 
 
+def test_film_lrelu_cpu_path_and_guards(pkg):
+    """film_lrelu on CPU tensors (and for every module it has no fused kernel for) is exactly act(film(x, t)); the fused route is
+    only taken for registered LReLu classes whose forward is the registered one."""
+    from pregenerating_pde_b200 import cno_model
+    torch.manual_seed(2)
+    film = cno_model.FILM(4, dim=[2, 3], s=16)
+    act = cno_model.lrelu_for(4, 16, 8)
+    with torch.no_grad():
+        for p_ in list(film.parameters()) + [act.bias]:
+            p_.add_(0.2 * torch.randn_like(p_))
+    x, t = torch.randn(2, 4, 16, 16, requires_grad=True), torch.rand(2)
+    y = pkg.cin.film_lrelu(film, act, x, t)
+    y2 = act(film(x, t))
+    assert torch.equal(y, y2) and 'FilmLRelu' not in type(y.grad_fn).__name__
+    g = torch.autograd.grad(y.square().sum(), [x] + list(film.parameters()) + [act.bias])
+    g2 = torch.autograd.grad(y2.square().sum(), [x] + list(film.parameters()) + [act.bias])
+    assert all(torch.equal(a, b) for a, b in zip(g, g2))
+    # registration: the mirror's LReLu is registered with its own forward; a subclass or a replaced forward is not
+    assert pkg.cin._lrelu_forward_of(act) is cno_model.LReLu.forward
+
+    class Other(cno_model.LReLu):
+        def forward(self, x):
+            return super().forward(x) * 2
+    o = Other(4, 4, 16, 8, **cno_model._filter_args(16, 8, 2.0001, 0.8))
+    assert pkg.cin._lrelu_forward_of(o) is None
+    assert torch.equal(pkg.cin.film_lrelu(film, o, x, t), o(film(x, t)))
+
+
 def test_missing_library_is_a_hard_error(pkg, monkeypatch):
     monkeypatch.setattr(pkg._lib, '_lib', None)
     monkeypatch.setattr(pkg._lib, 'LIB_PATH', '/nonexistent/libcno_b200.so')

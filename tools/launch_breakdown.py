@@ -17,7 +17,7 @@ for r in rd:
     us = v / 1e3 if u in ('ns', 'nsecond') else v * (1e3 if u in ('ms', 'msecond') else 1.0)
     rows.append((r[ki], us))
 names = [n for n, _ in rows]
-period = None
+period, whole = None, False
 for P in range(200, len(names) // 2):
     if names[-P:] == names[-2 * P:-P]:
         period = P
@@ -25,9 +25,11 @@ for P in range(200, len(names) // 2):
 if period is None:                     # e.g. a list cut by ncu's -c limit: summarise everything that was captured
     print('no repeating step found: summarising the whole list')
     period = len(rows)
+    whole = True
 step = rows[-period:]
 tot = sum(us for _, us in step)
-print(f'one CNO_time training step (eager, ncu per-launch times: cold cache, serialised): {period} launches, sum {tot / 1e3:.2f} ms')
+print(('whole launch list' if whole else 'one CNO_time training step (eager)') +
+      f' - ncu per-launch times (cold cache, serialised): {period} launches, sum {tot / 1e3:.2f} ms')
 agg = collections.defaultdict(lambda: [0.0, 0])
 for n, us in step:
     agg[n][0] += us; agg[n][1] += 1
