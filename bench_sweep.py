@@ -20,6 +20,23 @@ DEV = 'cuda'
 POOL_BYTES = 384e6
 
 
+def ref_plugin(name):
+    """the reference's own CUDA plugin recompiled for sm_100a (oracle/build_ref_plugins.py), or None.
+    Baseline leg only: it is timed beside our kernel and never feeds a product path."""
+    if name not in _REF:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+            import build_ref_plugins
+            _REF[name] = build_ref_plugins.load(name)
+        except Exception as ex:                      # missing build, ABI mismatch, ...: the column stays empty
+            print(f'reference plugin {name} unavailable: {ex}', file=sys.stderr)
+            _REF[name] = None
+    return _REF[name]
+
+
+_REF = {}
+
+
 def peak():
     try:
         return json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))['hbm_gbs']
@@ -84,8 +101,29 @@ def sweep_filtered_lrelu(rows, N, C, s_in, s_out, dtype, reps):
                                         px0 - (tu - 1), py0 - (tu - 1), gg, slope, float('inf'), True, False, signs_only=True)
     cfgname = 'I' if s_in == s_out else ('D' if s_out < s_in else 'U')
     shape = f'[{N},{C},{s_in}->{s_out}] {cfgname}'
-    rows.append(row('filtered_lrelu', shape, dtype, 'fwd', time_graph(fwd, nrot, reps), nbytes))
-    rows.append(row('filtered_lrelu', shape, dtype, 'bwd', time_graph(bwd, nrot, reps), nbytes))
+    rf, rb = row('filtered_lrelu', shape, dtype, 'fwd', time_graph(fwd, nrot, reps), nbytes), None
+    rows.append(rf)
+    rb = row('filtered_lrelu', shape, dtype, 'bwd', time_graph(bwd, nrot, reps), nbytes)
+    rows.append(rb)
+    # the reference's CUDA kernel (StyleGAN3 filtered_lrelu.cu recompiled for sm_100a) on the same buffers: fp32 / fp16 only
+    ref = ref_plugin('filtered_lrelu_plugin') if dtype in (torch.float32, torch.float16) else None
+    if ref is not None:
+        inf = float('inf')
+        r_fwd = lambda i: ref.filtered_lrelu(xs[i % nrot], fu, fd, b, e, up, down, px0, px1, py0, py1, 0, 0, gain, slope, inf, False, True)
+        r_bwd = lambda i: ref.filtered_lrelu(dys[i % nrot], fd, fu, zb, masks[i % nrot], down, up, pp[0], pp[1], pp[2], pp[3],
+                                             px0 - (tu - 1), py0 - (tu - 1), gg, slope, inf, True, False)
+        yr, sor, rcr = r_fwd(0)
+        if rcr == 0:
+            dxr = r_bwd(0)[0]
+            dxo = bwd(0)[0]
+            den = lambda t_: float(t_.float().abs().max().clamp_min(1e-30))
+            rf.update(ref_cuda_us=round(time_graph(r_fwd, nrot, reps), 2), y_maxrel_vs_ref_cuda=float((y.float() - yr.float()).abs().max()) / den(yr),
+                      mask_bytes_differ_vs_ref_cuda=int((sor != so).sum()), mask_bytes=int(so.numel()))
+            rb.update(ref_cuda_us=round(time_graph(r_bwd, nrot, reps), 2), dx_maxrel_vs_ref_cuda=float((dxo.float() - dxr.float()).abs().max()) / den(dxr))
+            for r_ in (rf, rb):
+                r_['vs_ref_cuda'] = round(r_['ref_cuda_us'] / r_['us'], 3)
+        else:
+            rf['ref_cuda_us'] = rb['ref_cuda_us'] = None      # the reference has no specialised kernel for this call
 
 
 def sweep_upfirdn2d(rows, N, C, S, mode, dtype, reps):
@@ -223,6 +261,8 @@ def sweep_film_lrelu(rows, N, C, S, dtype, reps):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--quick', action='store_true')
+    ap.add_argument('--grid', action='store_true', help='also the full configs[1] grid: C in {16..256} x {128,64,32}^2 x {fp32,bf16}, I-config')
+    ap.add_argument('--only', default='', help='comma list of op groups: flr,wide,up,bias,cin,pair (default: all)')
     ap.add_argument('--out', default=os.path.join(ROOT, 'profiles', 'sweep_latest.json'))
     ap.add_argument('--sweep', action='store_true')      # accepted when called through bench.py --sweep
     args, _ = ap.parse_known_args()
@@ -231,31 +271,48 @@ def main():
     rows = []
     levels = [(16, 128), (32, 64), (64, 32), (128, 16), (256, 8)]          # (C, H) of the CNO U-Net levels
     dtypes = [torch.float32] if args.quick else [torch.float32, torch.bfloat16]
+    only = set(filter(None, args.only.split(',')))
+    want = lambda g: not only or g in only
     for dt in dtypes:
         reps = 10
-        sweep_filtered_lrelu(rows, N, 64, 128, 128, dt, reps)             # the bench.py workload (lift / project shape)
-        for C, H in levels:
-            sweep_filtered_lrelu(rows, N, C, H, H, dt, reps)              # I
-        for (C, H) in [(32, 128), (64, 64), (128, 32), (256, 16)]:
-            sweep_filtered_lrelu(rows, N, C, H, H // 2, dt, reps)         # D
-        for (C, H) in [(128, 8), (64, 16), (32, 32), (16, 64)]:
-            sweep_filtered_lrelu(rows, N, C, H, H * 2, dt, reps)          # U
-        for C, H in [(64, 128), (16, 128), (64, 32)]:
-            sweep_upfirdn2d(rows, N, C, H, 'up2', dt, reps)
-            sweep_upfirdn2d(rows, N, C, H, 'down2', dt, reps)
-        for C, H in [(64, 128), (64, 32)]:
-            sweep_bias_act(rows, N, C, H, dt, reps)
-        for C, H in levels + [(64, 128)]:
-            sweep_cin(rows, N, C, H, dt, reps)
-        sweep_cin(rows, 8, 64, 256, dt, reps)                                 # wide fine-tune planes: thread-block cluster kernels
-        for C, H in [(64, 128), (16, 128), (64, 32)]:
-            sweep_film_lrelu(rows, N, C, H, dt, reps)                         # CIN -> filtered_lrelu prologue fusion
+        if want('flr'):
+            sweep_filtered_lrelu(rows, N, 64, 128, 128, dt, reps)             # the bench.py workload (lift / project shape)
+            for C, H in levels:
+                sweep_filtered_lrelu(rows, N, C, H, H, dt, reps)              # I
+            for (C, H) in [(32, 128), (64, 64), (128, 32), (256, 16)]:
+                sweep_filtered_lrelu(rows, N, C, H, H // 2, dt, reps)         # D
+            for (C, H) in [(128, 8), (64, 16), (32, 32), (16, 64)]:
+                sweep_filtered_lrelu(rows, N, C, H, H * 2, dt, reps)          # U
+        if want('wide'):                                                      # BASELINE.json configs[4]: 256^2 fine-tune planes
+            sweep_filtered_lrelu(rows, 8, 64, 256, 256, dt, reps)
+            sweep_filtered_lrelu(rows, 8, 64, 256, 128, dt, reps)
+            sweep_filtered_lrelu(rows, 8, 32, 128, 256, dt, reps)
+        if args.grid:                                                         # BASELINE.json configs[1]: the whole C x size grid
+            for H in (128, 64, 32):
+                for C in (16, 32, 64, 128, 256):
+                    if not any(r['shape'] == f'[{N},{C},{H}->{H}] I' and r['dtype'] == str(dt).replace('torch.', '') for r in rows):
+                        sweep_filtered_lrelu(rows, N, C, H, H, dt, reps)
+        if want('up'):
+            for C, H in [(64, 128), (16, 128), (64, 32)]:
+                sweep_upfirdn2d(rows, N, C, H, 'up2', dt, reps)
+                sweep_upfirdn2d(rows, N, C, H, 'down2', dt, reps)
+        if want('bias'):
+            for C, H in [(64, 128), (64, 32)]:
+                sweep_bias_act(rows, N, C, H, dt, reps)
+        if want('cin'):
+            for C, H in levels + [(64, 128)]:
+                sweep_cin(rows, N, C, H, dt, reps)
+            sweep_cin(rows, 8, 64, 256, dt, reps)                             # wide fine-tune planes: thread-block cluster kernels
+        if want('pair'):
+            for C, H in [(64, 128), (16, 128), (64, 32)]:
+                sweep_film_lrelu(rows, N, C, H, dt, reps)                     # CIN -> filtered_lrelu prologue fusion
     out = dict(gpu=torch.cuda.get_device_name(0), hbm_peak_gbs=peak(), rows=rows)
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     json.dump(out, open(args.out, 'w'), indent=1)
-    print(f'{"op":28s} {"shape":26s} {"dtype":9s} {"dir":4s} {"us":>9s} {"GB/s":>8s} {"frac":>6s}')
+    print(f'{"op":28s} {"shape":26s} {"dtype":9s} {"dir":4s} {"us":>9s} {"GB/s":>8s} {"frac":>6s} {"ref_cuda_us":>12s} {"x":>6s}')
     for r in rows:
-        print(f'{r["op"]:28s} {r["shape"]:26s} {r["dtype"]:9s} {r["dir"]:4s} {r["us"]:9.2f} {r["gbs"]:8.1f} {r["frac_hbm"]:6.3f}')
+        extra = f' {r["ref_cuda_us"]:12.2f} {r["vs_ref_cuda"]:6.2f}' if r.get('ref_cuda_us') else ''
+        print(f'{r["op"]:28s} {r["shape"]:26s} {r["dtype"]:9s} {r["dir"]:4s} {r["us"]:9.2f} {r["gbs"]:8.1f} {r["frac_hbm"]:6.3f}{extra}')
 
 
 if __name__ == '__main__':

@@ -597,13 +597,14 @@ int cin_launch(CinParams p, cudaStream_t st) {
     constexpr int V = 16 / sizeof(T);
     // 16-byte vectors per thread: bounded by the 64 registers a 1024-thread CTA leaves each thread (16-bit types unpack to twice
     // as many fp32 values per vector, so they hold half as many)
+    static EnvFlag env_no_stats, env_no_cluster;
     constexpr int VPT = (BWD ? 4 : 8) / (sizeof(T) == 2 ? 2 : 1);
     const bool vec_ok = (p.hw % V == 0) && !(((uintptr_t)p.x | (uintptr_t)p.y | (uintptr_t)p.dy | (uintptr_t)p.res) & 15u);
     const int nvec = p.hw / V;
     int gs = 8;
     while (gs < 1024 && (int64_t)gs * VPT < nvec) gs <<= 1;
     if constexpr (!BWD) {
-        if (!p.y && vec_ok && nvec >= STATS_MIN_VEC && !getenv("CNO_CIN_NO_STATS_KERNEL")) {
+        if (!p.y && vec_ok && nvec >= STATS_MIN_VEC && !env_no_stats.on("CNO_CIN_NO_STATS_KERNEL")) {
             cin_stats_kernel<T><<<(unsigned)p.planes, CTA, 0, st>>>(p);
             CNO_LAUNCH_CHECK();
             return 0;
@@ -616,7 +617,7 @@ int cin_launch(CinParams p, cudaStream_t st) {
         const int64_t blocks = (p.planes + ppc - 1) / ppc;
         if constexpr (BWD) cin_bwd_reg_kernel<T, VPT><<<(unsigned)blocks, threads, 0, st>>>(p);
         else cin_fwd_reg_kernel<T, VPT><<<(unsigned)blocks, threads, 0, st>>>(p);
-    } else if (vec_ok && (int64_t)8 * CLUSTER_CTA * VPT >= nvec && p.planes * 8 < (1ll << 31) && !getenv("CNO_CIN_NO_CLUSTER")) {
+    } else if (vec_ok && (int64_t)8 * CLUSTER_CTA * VPT >= nvec && p.planes * 8 < (1ll << 31) && !env_no_cluster.on("CNO_CIN_NO_CLUSTER")) {
         // thread-block cluster of 2 / 4 / 8 CTAs per plane (portable cluster size limit: 8)
         int cs = 2;
         while ((int64_t)cs * CLUSTER_CTA * VPT < nvec) cs <<= 1;

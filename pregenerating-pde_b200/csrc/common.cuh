@@ -6,6 +6,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 #include "../../include/cno_b200.h"
 
 #ifndef __CUDA_ARCH__
@@ -17,6 +18,30 @@ void cno_set_error(const char* fmt, ...);
 #define CNO_CHECK_ARG(cond, ...) do { if (!(cond)) { cno_set_error(__VA_ARGS__); return (int)cudaErrorInvalidValue; } } while (0)
 #define CNO_LAUNCH_CHECK() do { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { \
     cno_set_error("%s:%d CUDA launch failed: %s", __FILE__, __LINE__, cudaGetErrorString(e_)); return (int)e_; } } while (0)
+
+// ---- per-device launch caches ---------------------------------------------------------------------
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) and occupancy answers belong to ONE device: a process that drives several
+// GPUs (torch.cuda.device(i) around the calls) needs them per ordinal, and the forward thread and the autograd thread may
+// race on them, hence atomics.  Each kernel instantiation owns one DevSmemOptIn (function-local static).
+#include <atomic>
+constexpr int CNO_MAX_DEVICES = 64;
+static inline int cno_current_device() { int d = 0; if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= CNO_MAX_DEVICES) d = 0; return d; }
+struct DevSmemOptIn {
+    std::atomic<size_t> bytes[CNO_MAX_DEVICES];
+    // raises the kernel's dynamic shared memory limit on the current device when `need` exceeds what was configured there
+    template <class K> cudaError_t ensure(K kern, size_t need) {
+        const int d = cno_current_device();
+        if (need <= bytes[d].load(std::memory_order_acquire)) return cudaSuccess;
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
+        if (e == cudaSuccess) { size_t cur = bytes[d].load(); while (cur < need && !bytes[d].compare_exchange_weak(cur, need)) {} }
+        return e;
+    }
+};
+// one cached environment switch (read once per process instead of a getenv() per launch)
+struct EnvFlag {
+    std::atomic<int> v{-1};
+    bool on(const char* name) { int x = v.load(std::memory_order_relaxed); if (x < 0) { x = getenv(name) ? 1 : 0; v.store(x); } return x != 0; }
+};
 
 static inline int cno_dtype_size(int dt) { return dt == CNO_F32 ? 4 : dt == CNO_F64 ? 8 : 2; }
 

@@ -118,6 +118,9 @@ struct Params {
     int tmaX, xshift;          // TMA start column = cminX rounded down to a 16-byte boundary (the hardware faults on an
                                // unaligned innermost coordinate; measured, tools/probes/tma_probe.cu); xshift = cminX - tmaX
     int bwx;                   // x tile row pitch (elements) = TMA box width
+    int nbox, bstep;           // planes wider than one TMA box (256 elements) are staged as nbox boxes of bwx columns whose start
+                               // columns are bstep = bwx - 16 apart (16 columns of overlap, so every thread finds its whole
+                               // window inside ONE box); smem stage layout [nbox][P][RS][bwx]
     int dp, dq;                // D row pitch in floats = 4 * DOWN * dq.  A finished row is stored as DOWN interleaved classes:
                                // float4 f sits at float4 position (f / DOWN) + (f % DOWN) * dq, dq = 8 / DOWN (mod 8), so that the
                                // writers (consecutive f) and the h-down readers (f = DOWN*cq + i) are both bank-conflict free and
@@ -196,6 +199,7 @@ struct Stream {
     f2 bE[2];               // bias times the horizontal edge profile of the up-FIR
     f2 aff2;                // AFF: (a, a) of this thread's plane
     int unit, g;            // plane slot in the CTA, column group
+    int xofs;               // element offset of this thread's first x sample inside its unit's tile row (includes the box offset)
     int dofs;               // float offset of this thread's float4 inside a D row
     bool active;
     uint32_t colmask;       // WRITE: valid-column bits; READ: valid mask-element bits
@@ -210,6 +214,11 @@ struct Stream {
     FLR_DEV void init(const Params& p, const CtaGeom& cg, int tid, LD ld_bias) {
         unit = tid / p.G; g = tid - unit * p.G;
         dofs = 4 * dpos<C>(p, g);
+        {
+            const int xoff = ((C::UP == 2) ? 2 * g : g) + p.xshift;
+            int bi = xoff / p.bstep; if (bi > p.nbox - 1) bi = p.nbox - 1;
+            xofs = bi * (p.P * C::RS * p.bwx) + (xoff - bi * p.bstep);
+        }
         const int plane = cg.plane0 + unit;
         active = unit < p.P && plane < p.NC;
         FLR_UNROLL for (int r = 0; r < C::ND; r++) { acc[r][0] = mk2(0.f, 0.f); acc[r][1] = mk2(0.f, 0.f); }
@@ -258,10 +267,10 @@ struct Stream {
     // horizontal polyphase up-FIR of one staged input row -> two column pairs
     FLR_DEV void hup(const Params& p, const T* xrow /* tile row of this unit */, bool rowvalid, f2 out[2]) {
         float xs[8];
-        const int xoff = ((C::UP == 2) ? 2 * g : g) + p.xshift;
+        const int xoff = xofs;
 #if defined(__CUDA_ARCH__)
         if (C::UP == 2 && sizeof(T) == 4) {          // LDS.64 from the even column at or below xoff
-            if (xoff & 1) {                          // uniform branch (xshift is a launch constant): LDS.32, 3 x LDS.64, LDS.32
+            if (p.xshift & 1) {                      // uniform branch (the parity of xofs is that of xshift: 2g and bstep are even): LDS.32, 3 x LDS.64, LDS.32
                 xs[0] = xrow[xoff];
                 FLR_UNROLL for (int w = 0; w < 3; w++) { const float2 v = *reinterpret_cast<const float2*>(xrow + xoff + 1 + 2 * w); xs[1 + 2 * w] = v.x; xs[2 + 2 * w] = v.y; }
                 xs[7] = xrow[xoff + 7];

@@ -79,7 +79,8 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(ok ? 4 : 0) : "memory");
     };
     const int tid = threadIdx.x;
-    const uint32_t stage_tx = (uint32_t)(p.P * C::RS * p.bwx * (int)sizeof(T));
+    const uint32_t box_bytes = (uint32_t)(p.P * C::RS * p.bwx * (int)sizeof(T));
+    const uint32_t stage_tx = box_bytes * (uint32_t)p.nbox;
 
     if (tid == 0) {
         for (int i = 0; i < NSTAGE; i++) mbar_init(&bars[i], 1);
@@ -115,7 +116,8 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         auto issue = [&](int s) {
             const int slot = (gs0 + s) % NSTAGE;
             mbar_expect_tx(&bars[slot], stage_tx);
-            tma_load_3d(xst + (size_t)slot * p.stage_bytes, &tmap, &bars[slot], p.tmaX, cg.row0 + s * C::RS, cg.plane0);
+            for (int bx = 0; bx < p.nbox; bx++)
+                tma_load_3d(xst + (size_t)slot * p.stage_bytes + (size_t)bx * box_bytes, &tmap, &bars[slot], p.tmaX + bx * p.bstep, cg.row0 + s * C::RS, cg.plane0);
         };
         if (tid == 0) while (next_load < cg.nstages_total && next_load < NSTAGE) issue(next_load++);
 
@@ -204,20 +206,25 @@ inline int env_ctas() {
 template <class T, class C, int MODE, bool AFF = false>
 int launch_variant(const Plan& plan, const CUtensorMap& map, cudaStream_t st) {
     auto kern = flr_fused_kernel<T, C, MODE, AFF>;
-    static size_t configured = 0;      // per instantiation
-    if (plan.smem_bytes > configured) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem_bytes);
+    static DevSmemOptIn optin;         // per instantiation, per device
+    {
+        cudaError_t e = optin.ensure(kern, plan.smem_bytes);
         if (e != cudaSuccess) { cno_set_error("filtered_lrelu: cannot reserve %zu bytes of shared memory: %s", plan.smem_bytes, cudaGetErrorString(e)); return (int)e; }
-        configured = plan.smem_bytes;
     }
-    // persistent grid: one CTA per resident slot (occupancy x SM count), cached per (threads, smem)
-    static int occ_threads = 0, occ_ctas = 0; static size_t occ_smem = 0;
-    if (occ_threads != plan.threads || occ_smem != plan.smem_bytes) {
-        int per_sm = 0, dev = 0, sms = 148;
-        cudaGetDevice(&dev);
+    // persistent grid: one CTA per resident slot (occupancy x SM count), cached per device for the last (threads, smem) asked
+    struct Occ { std::atomic<uint64_t> key{0}; std::atomic<int> ctas{0}; };
+    static Occ occ[CNO_MAX_DEVICES];
+    const int dev = cno_current_device();
+    const uint64_t key = ((uint64_t)plan.threads << 32) | (uint64_t)plan.smem_bytes;
+    int occ_ctas = occ[dev].ctas.load(std::memory_order_acquire);
+    if (occ[dev].key.load(std::memory_order_acquire) != key || occ_ctas == 0) {
+        int per_sm = 0, sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, plan.threads, plan.smem_bytes) != cudaSuccess || per_sm < 1) per_sm = 1;
-        occ_ctas = per_sm * sms; occ_threads = plan.threads; occ_smem = plan.smem_bytes;
+        occ_ctas = per_sm * sms;
+        occ[dev].key.store(0, std::memory_order_release);      // invalidate, publish the value, then the key
+        occ[dev].ctas.store(occ_ctas, std::memory_order_release);
+        occ[dev].key.store(key, std::memory_order_release);
     }
     Plan pl = plan;
     if (env_ctas() == 0) set_partition(pl, occ_ctas);

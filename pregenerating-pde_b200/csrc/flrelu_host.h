@@ -83,7 +83,12 @@ static inline int make_plan(Plan& plan, int elem_size, int n, int c, int in_h, i
     p.xshift = p.cminX - p.tmaX;
     int bwx = ((up == 2) ? 2 * p.G + 6 : p.G + 6) + p.xshift + 1;     // +1: the odd-xshift path reads one float2 further
     bwx = (bwx + epv - 1) / epv * epv;
-    if (bwx > 256) return -1;                                          // TMA box limit
+    p.nbox = 1; p.bstep = 1 << 30;
+    if (bwx > 256) {                                                   // TMA box limit: several overlapping boxes per row strip
+        p.bstep = 256 - 16;
+        p.nbox = (bwx - 16 + p.bstep - 1) / p.bstep;
+        bwx = 256;
+    }
     p.bwx = bwx;
     p.ncq = (out_w + 3) / 4;
     {   // D row layout (flrelu_core.h Params::dq): DOWN classes of dq float4 each
@@ -111,7 +116,7 @@ static inline int make_plan(Plan& plan, int elem_size, int n, int c, int in_h, i
         if (forced > 0 && forced < P) P = forced;
     }
     for (;; P--) {
-        const size_t stage = ((size_t)P * rs * bwx * elem_size + 127) / 128 * 128;
+        const size_t stage = ((size_t)p.nbox * P * rs * bwx * elem_size + 127) / 128 * 128;
         const size_t total = NSTAGE * stage + (size_t)NDBUF * P * 6 * p.dp * 4 + 64 + (size_t)2 * P * (6 * down) * mstride + 16;   // +16: read_code loads one word past a row
         if (total <= FLR_SMEM_KB * 1024 || P == 1) { p.stage_bytes = (int)stage; plan.smem_bytes = total; break; }
     }

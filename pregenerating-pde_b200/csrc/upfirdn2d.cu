@@ -114,7 +114,8 @@ extern "C" int cno_upfirdn2d(const void* x, void* y, const float* f, int dtype, 
     CNO_CHECK_ARG(in_h >= 1 && in_w >= 1, "upfirdn2d: empty input plane");
     if (planes <= 0 || out_h <= 0 || out_w <= 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
-    if (separable && upx == upy && downx == downy && fw == fh && !getenv("CNO_UPFIRDN_GENERIC")) {
+    static EnvFlag env_generic;
+    if (separable && upx == upy && downx == downy && fw == fh && !env_generic.on("CNO_UPFIRDN_GENERIC")) {
         // fast path: compile-time polyphase arithmetic, register windows (upfirdn2d_fast.cuh)
         upfast::Params q{};
         q.x = x; q.y = y; q.f = f; q.in_h = in_h; q.in_w = in_w; q.out_h = out_h; q.out_w = out_w;

@@ -219,12 +219,11 @@ int launch(Params p, int64_t planes, cudaStream_t st) {
     const int64_t blocks = planes * p.tiles_x * p.tiles_y;
     if (blocks >= (1ll << 31)) { cno_set_error("upfirdn2d: grid too large"); return (int)cudaErrorInvalidValue; }
     auto kern = upfirdn2d_fast_kernel<T, UP, DOWN, NT, SMALL>;
-    static bool configured = false;
-    if (!configured && G::SMEM > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
+    static DevSmemOptIn optin;                 // per instantiation, per device
+    if (G::SMEM > 48 * 1024) {
+        cudaError_t e = optin.ensure(kern, G::SMEM);
         if (e != cudaSuccess) { cno_set_error("upfirdn2d: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e)); return (int)e; }
     }
-    configured = true;
     kern<<<(unsigned)blocks, G::THREADS, G::SMEM, st>>>(p);
     CNO_LAUNCH_CHECK();
     return 0;

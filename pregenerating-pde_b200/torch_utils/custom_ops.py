@@ -7,6 +7,7 @@ argument as in bias_act.cpp:24, upfirdn2d.cpp:8, filtered_lrelu.cpp:8/:205) boun
 library, so the reference's own op wrappers run on top of it unchanged, and so do ours.
 """
 import ctypes
+import weakref
 import numpy as np
 import torch
 
@@ -38,20 +39,26 @@ def _dense(t):
     return True
 
 
-_host_taps = {}
+def _same_layout(a, b):
+    """bias_act.cpp:8-20 has_same_layout: strides are compared only on dimensions of size >= 2"""
+    return all(a.size(i) == b.size(i) and (a.size(i) < 2 or a.stride(i) == b.stride(i)) for i in range(a.ndim))
+
+
+_host_taps = {}     # id(tensor) -> (weakref to the tensor, version, host copy)
 
 
 def host_taps(f):
-    """fp32 taps of a (constant) device filter on the host, cached per (storage, version) so the hot path
-    never synchronises."""
-    key = (f.data_ptr(), f._version, tuple(f.shape), f.device)
+    """fp32 taps of a (constant) device filter on the host, so the hot path never synchronises.
+    The copy is cached per tensor OBJECT (identity checked through a weak reference whose callback drops the entry)
+    together with its version counter: a freed filter whose storage the caching allocator hands to the next filter can
+    never alias an entry (an address-keyed cache did), and an in-place update of the filter invalidates the copy."""
+    key = id(f)
     hit = _host_taps.get(key)
-    if hit is None:
-        if len(_host_taps) > 256:
-            _host_taps.clear()
-        hit = np.ascontiguousarray(f.detach().to('cpu', torch.float32).numpy())
-        _host_taps[key] = hit
-    return hit
+    if hit is not None and hit[0]() is f and hit[1] == f._version:
+        return hit[2]
+    taps = np.ascontiguousarray(f.detach().to('cpu', torch.float32).numpy())
+    _host_taps[key] = (weakref.ref(f, lambda _r, k=key: _host_taps.pop(k, None)), f._version, taps)
+    return taps
 
 
 class _BiasActPlugin:
@@ -67,7 +74,7 @@ class _BiasActPlugin:
             if t.numel() and t.dtype != x.dtype:
                 raise RuntimeError(f'{name} must have the same dtype as x')
         for name, t in (('xref', xref), ('yref', yref), ('dy', dy)):
-            if t.numel() and (t.shape != x.shape or t.stride() != x.stride()):
+            if t.numel() and (t.shape != x.shape or not _same_layout(t, x)):
                 raise RuntimeError(f'{name} must have the same shape and layout as x')
         if b.numel() and (b.ndim != 1 or not (0 <= dim < x.ndim) or b.shape[0] != x.shape[dim]):
             raise RuntimeError('b must be a vector matching dimension `dim` of x')

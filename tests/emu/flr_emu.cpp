@@ -12,15 +12,18 @@ template <class C, int MODE, bool AFF = false>
 static void run(const Plan& plan, const float* x, float* y, const float* bias) {
     const Params& p = plan.p;
     const int nthreads = plan.threads;
-    std::vector<float> xst((size_t)NSTAGE * p.P * C::RS * p.bwx);
+    const size_t stage_el = (size_t)p.nbox * p.P * C::RS * p.bwx;
+    std::vector<float> xst((size_t)NSTAGE * stage_el);
     std::vector<float> D((size_t)2 * p.P * C::KO * p.dp, NAN);   // NaN: catches reads of unwritten cells
     auto tma = [&](int slot, int row, int plane0) {
-        float* dst = xst.data() + (size_t)slot * p.P * C::RS * p.bwx;
-        for (int u = 0; u < p.P; u++) for (int r = 0; r < C::RS; r++) for (int cidx = 0; cidx < p.bwx; cidx++) {
-            const int pl = plane0 + u, gy = row + r, gx = p.tmaX + cidx;
-            float v = 0.f;
-            if (pl < p.NC && gy >= 0 && gy < p.H && gx >= 0 && gx < p.W) v = x[((size_t)pl * p.H + gy) * p.W + gx];
-            dst[((size_t)u * C::RS + r) * p.bwx + cidx] = v;
+        for (int bx = 0; bx < p.nbox; bx++) {
+            float* dst = xst.data() + (size_t)slot * stage_el + (size_t)bx * p.P * C::RS * p.bwx;
+            for (int u = 0; u < p.P; u++) for (int r = 0; r < C::RS; r++) for (int cidx = 0; cidx < p.bwx; cidx++) {
+                const int pl = plane0 + u, gy = row + r, gx = p.tmaX + bx * p.bstep + cidx;
+                float v = 0.f;
+                if (pl < p.NC && gy >= 0 && gy < p.H && gx >= 0 && gx < p.W) v = x[((size_t)pl * p.H + gy) * p.W + gx];
+                dst[((size_t)u * C::RS + r) * p.bwx + cidx] = v;
+            }
         }
     };
     const size_t mbuf = (size_t)p.P * C::PB * p.mstride;
@@ -41,14 +44,14 @@ static void run(const Plan& plan, const float* x, float* y, const float* bias) {
             if (FLR_IS_READ(MODE)) for (int t = 0; t < nthreads; t++) stage_mask<C>(p, cg, cg.j_b0, t, nthreads, M.data(), copy4);
             for (int t = 0; t < nthreads; t++) {
                 th[t].init(p, cg, t, [&](int ch) { return bias[ch]; });
-                if (th[t].active) th[t].prologue(p, xst.data() + ((size_t)(gs0 % NSTAGE) * p.P + th[t].unit) * C::RS * p.bwx, cg.row0);
+                if (th[t].active) th[t].prologue(p, xst.data() + (size_t)(gs0 % NSTAGE) * stage_el + (size_t)th[t].unit * C::RS * p.bwx, cg.row0);
             }
             for (int k = 0; k < cg.nbodies; k++) {
                 const int s = 1 + k / C::M, slot = (gs0 + s) % NSTAGE;
                 if (FLR_IS_READ(MODE) && k + 1 < cg.nbodies) for (int t = 0; t < nthreads; t++)
                     stage_mask<C>(p, cg, cg.j_b0 + (k + 1) * C::PB, t, nthreads, M.data() + (size_t)((k + 1) & 1) * mbuf, copy4);
                 for (int t = 0; t < nthreads; t++) if (th[t].active)
-                    th[t].body(p, xst.data() + (size_t)slot * p.P * C::RS * p.bwx + ((size_t)th[t].unit * C::RS + (k % C::M) * C::PQ) * p.bwx,
+                    th[t].body(p, xst.data() + (size_t)slot * stage_el + ((size_t)th[t].unit * C::RS + (k % C::M) * C::PQ) * p.bwx,
                                cg.row0 + s * C::RS + (k % C::M) * C::PQ, cg.j_b0 + k * C::PB,
                                D.data() + ((size_t)(k & 1) * p.P + th[t].unit) * C::KO * p.dp,
                                M.data() + (size_t)(k & 1) * mbuf + (size_t)th[t].unit * C::PB * p.mstride);

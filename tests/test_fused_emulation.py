@@ -56,6 +56,8 @@ CASES = [  # name, in, out, N, C, forced number of persistent CTAs (0 = heuristi
     ('I', 32, 32, 1, 5, 0), ('D', 32, 16, 1, 2, 0), ('U', 16, 32, 1, 2, 0),
     ('I', 64, 64, 1, 2, 2), ('D', 64, 32, 1, 2, 3), ('U', 32, 64, 1, 3, 5), ('I', 128, 128, 1, 1, 4),
     ('I', 8, 8, 3, 40, 0), ('I', 32, 32, 2, 9, 7), ('U', 16, 32, 2, 9, 11), ('D', 32, 16, 3, 7, 6),
+    # planes wider than one 256-element TMA box (BASELINE.json configs[4], 256^2 fine-tune): several overlapping boxes per strip
+    ('I', 256, 256, 1, 2, 3), ('D', 256, 128, 1, 1, 2), ('U', 128, 256, 1, 1, 2), ('I', 512, 512, 1, 1, 5),
 ]
 
 

@@ -23,6 +23,12 @@ T = lambda a: torch.from_numpy(np.asarray(a))
 DEV = 'cuda'
 
 
+def report(section, entry):
+    """per-row numbers for the parity report (tests/conftest.py writes it to gpurun_out/parity_report.json at session end)"""
+    import conftest
+    conftest.PARITY_REPORT.setdefault(section, []).append(entry)
+
+
 def rel(a, b):
     a, b = a.detach().double().cpu(), b.detach().double().cpu()
     return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
@@ -71,7 +77,9 @@ def test_filtered_lrelu_golden(cno, golden, name):
 
 SWEEP = [('I', 128, 128, 2, 5), ('D', 128, 64, 2, 3), ('U', 64, 128, 2, 3), ('I', 64, 64, 3, 9), ('D', 64, 32, 1, 8),
          ('U', 32, 64, 2, 4), ('I', 32, 32, 2, 16), ('I', 16, 16, 2, 32), ('D', 16, 8, 2, 32), ('U', 8, 16, 2, 32),
-         ('I', 8, 8, 4, 64)]
+         ('I', 8, 8, 4, 64),
+         # BASELINE.json configs[4] (wide fine-tune, 256^2 planes) and one 512^2 case: planes wider than one TMA box
+         ('I', 256, 256, 2, 4), ('D', 256, 128, 1, 3), ('U', 128, 256, 1, 3), ('I', 512, 512, 1, 2)]
 
 
 @pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16, torch.float16])
@@ -85,16 +93,28 @@ def test_filtered_lrelu_sweep(cno, name, s_in, s_out, N, C, dtype):
     xr, br = x.clone().requires_grad_(True), b.clone().requires_grad_(True)
     y_ref = O.filtered_lrelu(xr, cfg['fu'], cfg['fd'], br, up=cfg['up'], down=cfg['down'], padding=cfg['padding'])
     dx_ref, db_ref = torch.autograd.grad(y_ref, [xr, br], dy)
+    # every CNO configuration, forward and backward shape, must run on the fused kernel (no silent generic composition)
+    lib = cno._lib.load()
+    dti = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2}[dtype]
+    tu, td, pad = len(cfg['fu']), len(cfg['fd']), cfg['padding']
+    assert lib.cno_filtered_lrelu_query(dti, s_in, s_in, s_out, s_out, tu, td, cfg['up'], cfg['down'], pad[0], pad[2]) == 0
+    assert lib.cno_filtered_lrelu_query(dti, s_out, s_out, s_in, s_in, td, tu, cfg['down'], cfg['up'], tu + td - 2 - pad[0], tu + td - 2 - pad[2]) == 0
     y, dx, db, mask = fl_case(cno, x, b, dy, cfg, dtype)
     assert y.dtype == dtype and dx.dtype == dtype
-    tol = 1e-5 if dtype == torch.float32 else 2e-2          # BASELINE.json tolerances
-    assert rel(y, y_ref) < tol and rel(dx, dx_ref) < tol and rel(db, db_ref) < (tol if dtype == torch.float32 else 3e-2)
+    tol = 1e-5 if dtype == torch.float32 else 2e-2          # BASELINE.json tolerances (y, dx and db alike)
+    errs = (rel(y, y_ref), rel(dx, dx_ref), rel(db, db_ref))
     v = O.filtered_lrelu_preact(x, cfg['fu'], b, up=cfg['up'], padding=cfg['padding'])
     sh, swb, swv = O.sign_mask_shape(y.shape[2:], cfg['fd'], cfg['down'])
     bad = O.unpack_sign_mask(mask.cpu(), swv) != O.sign_mask_from_preact(v, 0.2, math.sqrt(2), None, sh, swv)
-    assert int((bad & (v[:, :, :sh, :swv].abs() > 1e-5)).sum()) == 0
-    # at |v| <= 1e-5 the sign depends on the fp32 summation order; 16-bit inputs make such near-cancellations commoner
-    assert int(bad.sum()) <= (2 if dtype == torch.float32 else 16)
+    n_far, n_all = int((bad & (v[:, :, :sh, :swv].abs() > 1e-5)).sum()), int(bad.sum())
+    report('filtered_lrelu_sweep', dict(case=f'{name} [{N},{C},{s_in}->{s_out}]', dtype=str(dtype).replace('torch.', ''),
+                                        y=errs[0], dx=errs[1], db=errs[2], mask_elements=int(bad.numel()),
+                                        sign_mismatch_total=n_all, sign_mismatch_beyond_1e5=n_far))
+    assert max(errs) < tol, errs
+    assert n_far == 0
+    # at |v| <= 1e-5 the sign depends on the fp32 summation order (the oracle is itself 2e-7 from its fp64 evaluation,
+    # BASELINE.md section 3); the exact count of every row goes to the parity report, the cap scales with the mask size
+    assert n_all <= max(2 if dtype == torch.float32 else 16, bad.numel() // 100000)
 
 
 def test_filtered_lrelu_generic_golden(cno, golden):
@@ -656,3 +676,53 @@ def test_plugin_layer_matches_reference_signatures(cno):
     with pytest.raises(RuntimeError):
         P('filtered_lrelu_plugin').filtered_lrelu(x, cfg['fu'].to(DEV), cfg['fd'].to(DEV), b[:2], e, 2, 2, 11, 10, 11, 10, 0, 0,
                                                   1.0, 0.2, float('inf'), False, False)
+
+
+def test_filter_cache_survives_reallocation(cno):
+    """the host copy of a device filter must follow the tensor OBJECT, not its address.  Freed same-shape
+    filters get their storage re-used by the caching allocator; each new filter has different taps and must give its own result."""
+    g = torch.Generator().manual_seed(77)
+    x = torch.randn(1, 2, 16, 16, generator=g); b = torch.zeros(2)
+    pad = [11, 10, 11, 10]
+    ptrs = set()
+    for i in range(6):
+        fu = torch.randn(12, generator=g); fd = torch.randn(12, generator=g)
+        fu_d, fd_d = fu.to(DEV), fd.to(DEV)              # fresh device tensors; the previous ones were freed at the end of the last turn
+        ptrs.add(fu_d.data_ptr())
+        y = cno.filtered_lrelu.filtered_lrelu(x.to(DEV), fu_d, fd_d, b.to(DEV), up=2, down=2, padding=pad)
+        y_ref = O.filtered_lrelu(x, fu, fd, b, up=2, down=2, padding=pad)
+        assert rel(y, y_ref) < 1e-5, f'stale filter taps on allocation {i}'
+        # in-place update of a live filter invalidates the copy too
+        fu_d.mul_(0.5)
+        y2 = cno.filtered_lrelu.filtered_lrelu(x.to(DEV), fu_d, fd_d, b.to(DEV), up=2, down=2, padding=pad)
+        assert rel(y2, O.filtered_lrelu(x, fu * 0.5, fd, b, up=2, down=2, padding=pad)) < 1e-5
+        del fu_d, fd_d
+    assert len(ptrs) < 6, 'the allocator never re-used a block: the test did not exercise the aliasing case'
+
+
+def test_bias_act_size1_dims_noncanonical_stride(cno):
+    """layout equality ignores strides of size-1 dimensions (bias_act.cpp:8-20 has_same_layout)."""
+    plug = cno.custom_ops.get_plugin('bias_act_plugin')
+    x = torch.randn(1, 3, 5, 7, device=DEV)
+    dy = torch.as_strided(torch.randn(7, 3, 5, 7, device=DEV), x.shape, (210, 35, 7, 1))   # batch stride differs on the size-1 dimension
+    assert dy.stride() != x.stride() and dy.shape == x.shape
+    e = torch.empty(0)
+    b = torch.randn(3, device=DEV)
+    y = plug.bias_act(x, b, e, e, e, 0, 1, 3, 0.2, 1.0, -1)
+    dx = plug.bias_act(dy, e, e, y, e, 1, 1, 3, 0.2, 1.0, -1)     # must not raise "same shape and layout"
+    ref = torch.where(y > 0, dy, 0.2 * dy)
+    assert rel(dx, ref) < 1e-6
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs in one process')
+def test_two_devices_one_process(cno):
+    """the > 48 KB shared-memory opt-in and the occupancy cache are per device."""
+    cfg = O.lrelu_config(64, 64)
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(2, 3, 64, 64, generator=g); b = torch.randn(3, generator=g)
+    y_ref = O.filtered_lrelu(x, cfg['fu'], cfg['fd'], b, up=2, down=2, padding=cfg['padding'])
+    for dev in ('cuda:0', 'cuda:1', 'cuda:0'):
+        y = cno.filtered_lrelu.filtered_lrelu(x.to(dev), cfg['fu'].to(dev), cfg['fd'].to(dev), b.to(dev), up=2, down=2, padding=cfg['padding'])
+        up = cno.upfirdn2d.upsample2d(x.to(dev), cfg['fu'].to(dev), up=2)
+        assert rel(y, y_ref) < 1e-5
+        assert rel(up, O.upfirdn2d(x, cfg['fu'], up=2, padding=[6, 5, 6, 5], gain=4)) < 1e-5
