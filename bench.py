@@ -121,15 +121,21 @@ def run_reference_arm(args):
 
 
 def _finish(world, dev):
-    """Multi-rank exit.  Tearing down an NCCL communicator whose collectives live in captured CUDA graphs can block in the
-    communicator destructor (seen at 8 ranks), so after a last barrier every rank leaves without running destructors."""
+    """Multi-rank exit.  Round 1 left with os._exit because destroying the NCCL communicator blocked at 8 ranks: the captured
+    CUDA graphs that hold its kernels were still alive.  Now every graph is dropped first (Trainer.close / del), then the
+    process group is destroyed in order.  A watchdog thread still ends the process if teardown ever blocks, so a hang cannot
+    cost the driver its scaling run."""
     if world > 1:
         import torch.distributed as dist
         torch.cuda.synchronize(dev)
         dist.barrier()
         torch.cuda.synchronize(dev)
         sys.stdout.flush(); sys.stderr.flush()
-        os._exit(0)
+        t = threading.Timer(20.0, lambda: os._exit(0))
+        t.daemon = True
+        t.start()
+        dist.destroy_process_group()
+        t.cancel()
 
 
 def run_ours(args):
@@ -140,6 +146,9 @@ def run_ours(args):
     local = int(os.environ.get('LOCAL_RANK', '0'))
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
+    # CPU baseline first, on rank 0, while the other ranks sleep in the rendezvous below (a rank that spins in an NCCL
+    # barrier next to it took half the host cores away: 0.53 -> 0.28 GB/s at N >= 2 in round 1)
+    cpu_rec = time_cpu(8, 1, CPU_SAMPLE) if rank == 0 else None
     if world > 1:
         dist.init_process_group('nccl', device_id=dev)
     cno._lib.load()
@@ -258,11 +267,14 @@ def run_ours(args):
                 'bwd': dict(name='flr_fused_kernel<float, Cfg<2,2,1,1>, SIGN_READ> (backward, reads the sign mask, accumulates db)', ms=bwd_ms,
                             bytes=bb, traffic=ncu.get('flr_bwd_dram_bytes_per_launch'))}
         dom = 'bwd' if bwd_ms >= fwd_ms else 'fwd'
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        sm_max = (clocks or {}).get('sm_max_mhz') or 1965
+        fp32_floor_ms = W['N'] * W['C'] * 1234008 / (sms * 128 * sm_max * 1e6) * 1e3
         oth = 'fwd' if dom == 'bwd' else 'bwd'
         gbs = lambda k: kern[k]['bytes'] / (kern[k]['ms'] * 1e-3) / 1e9
         achieved = gbs(dom)
         traffic = kern[dom]['traffic']
-        cpu_gbs, cpu_dt, cores = time_cpu(8, 1, CPU_SAMPLE)
+        cpu_gbs, cpu_dt, cores = cpu_rec
         h2d = hx.numel() * 4 + hdy.numel() * 4 + hb.numel() * 4
         d2h = hdx.numel() * 4 + hdb.numel() * 4
         out = {
@@ -283,30 +295,51 @@ def run_ours(args):
                          'timing': 'CUDA events around K graph replays of the step and of the forward alone; backward = difference',
                          'other_kernel': {'kernel': kern[oth]['name'], 'achieved': round(gbs(oth), 1), 'frac': round(gbs(oth) / peak, 4),
                                           'avg_launch_ms': round(kern[oth]['ms'], 4), 'traffic': kern[oth]['traffic']},
-                         'fp32_pipe_note': 'op is 16.5 FLOP/B: the FP32 FMA pipe bounds this launch at 75.5 us = 0.62 of the HBM roofline '
-                                           '(DESIGN.md 3.1); ncu pipe_fma_cycles_active is reported in profiles/'},
+                         'traffic_source': 'profiles/ncu_traffic.json (dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this kernel; not re-measured in this run)',
+                         # the op is 16.5 FLOP/B: at fp32 the FMA pipe, not HBM, is the binding roof.  MACs per launch =
+                         # planes x 1,234,008; pipe peak = SMs x 128 lanes x max SM clock
+                         'fp32_pipe_floor_ms': round(fp32_floor_ms, 4), 'fp32_pipe_frac': round(fp32_floor_ms / kern[dom]['ms'], 4),
+                         'compound_frac': round(max(fp32_floor_ms, kern[dom]['bytes'] / peak / 1e6) / kern[dom]['ms'], 4),
+                         'compound_note': 'time / max(HBM time, FP32-FMA time): the ceiling of frac for a perfect CUDA-core kernel is '
+                                          f"{round(kern[dom]['bytes'] / peak / 1e6 / fp32_floor_ms, 3)}"},
             'cpu_baseline': {'value': round(cpu_gbs, 4), 'unit': 'GB/s', 'cores': cores, 'kind': 'port',
                              'sample': f"oracle port of impl='ref', fp32 [8,64,128,128] (1/4 of the batch), 8 timed passes, {cpu_dt * 1e3:.0f} ms each"},
             'clocks': clocks,
         }
+    # ---- BASELINE.json's second metric in the same line: CNO_time training samples/s (gradient all-reduce over NCCL at N > 1)
+    del g_step, g_fwd, pool, x, dy, hx, hdy, hdx
+    torch.cuda.empty_cache()
+    train_rec = None
+    if not args.no_train:
+        targs = argparse.Namespace(**vars(args)); targs.steps = max(3, min(args.steps, 20))
+        train_rec = measure_train(targs, world, rank, dev, mode='train')
+    if rank == 0:
+        out['cno_train'] = train_rec
         print(json.dumps(out), flush=True)
     _finish(world, dev)
 
 
-def run_cno_train(args):
-    """Secondary workload (BASELINE.json configs[2], [3]): CNO_time (TrainCNO_time_L configuration, 18.28 M parameters) training
-    step on synthetic FPO batches, batch 32 per GPU, DDP over NCCL for N > 1; value = samples/s over all GPUs."""
+def measure_train(args, world, rank, dev, mode='train'):
+    """CNO_time training step (TrainCNO_time_L configuration) or the wide fine-tune step (BASELINE.json configs[4]) on synthetic
+    batches, batch `args.batch` per GPU; returns the record rank 0 prints (None on the other ranks).  The process group is
+    already initialised by the caller when world > 1."""
     import torch.distributed as dist
     import pregenerating_pde_b200 as cno
-    world = int(os.environ.get('WORLD_SIZE', '1')); rank = int(os.environ.get('RANK', '0')); local = int(os.environ.get('LOCAL_RANK', '0'))
-    torch.cuda.set_device(local)
-    dev = torch.device('cuda', local)
-    if world > 1:
-        dist.init_process_group('nccl', device_id=dev)
     torch.backends.cudnn.benchmark = True
     B = args.batch
-    tr = cno.train.Trainer(device=dev, ddp=world > 1, graph=bool(args.graph))
-    batches = [cno.train.synthetic_fpo_batch(B, device='cpu', seed=100 * rank + i) for i in range(2)]
+    if mode == 'finetune':
+        ft = cno.finetune.wide_finetune_config()
+        tr = cno.train.Trainer(device=dev, ddp=world > 1, graph=bool(args.graph), mode='finetune', ft=ft,
+                               autocast=torch.bfloat16 if args.autocast == 'bf16' else None)
+        batches = [cno.train.synthetic_finetune_batch(B, ft, device='cpu', seed=100 * rank + i) for i in range(2)]
+        name = ('CNO_FineTune wide config: foundation CNO_time (in 5 / out 4, N_layers 4, N_res 8) at 256x256, channel_multiplier 64 '
+                '(features 32..512), initialize_FT(5->4 in, 4->3 out: 128x128 output), 3-group AdamW')
+    else:
+        tr = cno.train.Trainer(device=dev, ddp=world > 1, graph=bool(args.graph),
+                               autocast=torch.bfloat16 if args.autocast == 'bf16' else None)
+        batches = [cno.train.synthetic_fpo_batch(B, device='cpu', seed=100 * rank + i) for i in range(2)]
+        name = 'CNO_time TrainCNO_time_L config (N_layers 4, N_res 8, 18.28M params) fwd + rel-L1 + bwd + AdamW, FPO 7ch 128x128'
+    nparam = sum(p.numel() for p in tr.params)
     host = [tuple(v.pin_memory() for v in b) for b in batches]
     devb = [tuple(v.to(dev) for v in b) for b in batches]
 
@@ -316,7 +349,7 @@ def run_cno_train(args):
         torch.cuda.synchronize()
     for i in range(max(args.warmup, 3)):
         tr.step(*devb[i % 2])
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(dev.index or 0)
     if rank == 0:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -336,23 +369,44 @@ def run_cno_train(args):
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     ms, e2e_ms = tt.tolist()
+    rec = None
     if rank == 0:
         h2d = sum(v.numel() * v.element_size() for v in host[0])
-        print(json.dumps({
-            'metric': 'cno_train_samples_per_s', 'value': round(world * B / (ms * 1e-3), 2), 'unit': 'samples/s', 'n_gpus': world,
-            'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': round(ms, 3), 'higher_is_better': True, 'scaling': 'weak',
-            'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': {'workload': 'CNO_time TrainCNO_time_L config (N_layers 4, N_res 8, 18.28M params) fwd + rel-L1 + bwd + AdamW, FPO 7ch 128x128',
-                       'batch_per_gpu': B, 'cuda_graph': bool(tr.use_graph), 'parallelism': f'dp{world}', 'grad_allreduce': tr.dp_mode, 'final_loss': round(float(loss), 5)},
-            'e2e': {'value': round(world * B / (e2e_ms * 1e-3), 2), 'unit': 'samples/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 4,
-                    'ms_per_step': round(e2e_ms, 3)},
-            'clocks': clocks}), flush=True)
+        rec = {'metric': 'cno_train_samples_per_s' if mode == 'train' else 'cno_finetune_samples_per_s',
+               'value': round(world * B / (ms * 1e-3), 2), 'unit': 'samples/s', 'n_gpus': world,
+               'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': round(ms, 3), 'higher_is_better': True, 'scaling': 'weak',
+               'vs_baseline': None, 'dtype': 'bf16 autocast (convolutions), fp32 master weights' if args.autocast == 'bf16' else 'f32', 'data': 'synthetic',
+               'config': {'workload': name, 'parameters': nparam, 'batch_per_gpu': B, 'cuda_graph': bool(tr.use_graph), 'parallelism': f'dp{world}',
+                          'grad_allreduce': tr.dp_mode, 'grad_bytes': nparam * 4, 'final_loss': round(float(loss), 5)},
+               'e2e': {'value': round(world * B / (e2e_ms * 1e-3), 2), 'unit': 'samples/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 4,
+                       'ms_per_step': round(e2e_ms, 3)},
+               'clocks': clocks}
+    tr.close()
+    del tr
+    torch.cuda.empty_cache()
+    return rec
+
+
+def run_cno_train(args, mode='train'):
+    """Secondary workloads: `--workload cno_train` (BASELINE.json configs[2], [3]) and `--workload cno_finetune` (configs[4]) as
+    the headline of their own JSON line; value = samples/s over all GPUs."""
+    import torch.distributed as dist
+    world = int(os.environ.get('WORLD_SIZE', '1')); rank = int(os.environ.get('RANK', '0')); local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    rec = measure_train(args, world, rank, dev, mode=mode)
+    if rank == 0:
+        print(json.dumps(rec), flush=True)
     _finish(world, dev)
 
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument('--workload', default='flr', choices=['flr', 'cno_train'])
+    ap.add_argument('--workload', default='flr', choices=['flr', 'cno_train', 'cno_finetune'])
+    ap.add_argument('--autocast', default='none', choices=['none', 'bf16'])
+    ap.add_argument('--no-train', dest='no_train', action='store_true', help='flr workload: skip the cno_train sub-record')
     ap.add_argument('--batch', type=int, default=32)
     ap.add_argument('--graph', type=int, default=1)
     ap.add_argument('--gpus', type=int, default=1)
@@ -368,6 +422,10 @@ def main():
         return run_reference_arm(args)
     if args.workload == 'cno_train':
         return run_cno_train(args)
+    if args.workload == 'cno_finetune':
+        if args.batch == 32 and args.autocast == 'none':
+            args.autocast = 'bf16'                     # BASELINE.json configs[4]: bf16
+        return run_cno_train(args, mode='finetune')
     return run_ours(args)
 
 

@@ -193,7 +193,7 @@ def _film_fusable(self, x):
     return (all(isinstance(m, torch.nn.Linear) and m.bias is not None for m in lin)
             and self.inp2lat_sacale.in_features == 1 and self.inp2lat_bias.in_features == 1
             and self.inp2lat_sacale.out_features == self.inp2lat_bias.out_features
-            and all(m.weight.dtype == torch.float32 for m in lin) and not torch.is_autocast_enabled())
+            and all(m.weight.dtype == torch.float32 for m in lin))
 
 
 def film_forward(self, x, timestep, residual=None):

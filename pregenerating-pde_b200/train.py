@@ -46,55 +46,107 @@ def freeze_dead_parameters(model):
 
 
 class Trainer:
-    """One optimisation step = forward, relative L1 (CNO_timeModule_CIN.py:939), backward, (all-reduce), AdamW (:996)."""
+    """One optimisation step = forward, relative L1 (CNO_timeModule_CIN.py:939), backward, (all-reduce), AdamW (:996).
 
-    def __init__(self, cfg=None, device='cuda', ddp=False, graph=False, autocast=None, channels_last=False):
+    Data parallelism: batch sharding, the gradient all-reduce is the only exchange.  Every gradient lives in ONE
+    flat fp32 buffer (`p.grad` are views of it, laid out in reverse registration order = the order backward produces them), cut
+    into `buckets` contiguous ranges.  A post-accumulate hook counts the parameters of a bucket; when the last one has its
+    gradient the bucket's `ncclAllReduce(AVG)` is issued on a side stream, so it overlaps the rest of backward -- no
+    concatenation, no copy back, no scaling pass.  All of it is capturable: with `graph=True` the whole step (forward, backward,
+    bucketed all-reduces on the forked stream, AdamW) replays as one CUDA graph per rank.
+    `mode='finetune'`: CNO_FineTune.py workload (finetune.initialize_FT wrappers, three AdamW groups)."""
+
+    def __init__(self, cfg=None, device='cuda', ddp=False, graph=False, autocast=None, buckets=4, mode='train', ft=None):
         self.device = torch.device(device)
-        cfg = dict(cfg or cno_model.train_config_L())
-        self.model = cno_model.CNO_time(**cfg).to(self.device)
+        if mode == 'finetune':
+            from . import finetune
+            ft = ft or finetune.wide_finetune_config()
+            self.model = finetune.initialize_FT(cno_model.CNO_time(**ft['model']), **ft['ft']).to(self.device)
+        else:
+            cfg = dict(cfg or cno_model.train_config_L())
+            self.model = cno_model.CNO_time(**cfg).to(self.device)
         freeze_dead_parameters(self.model)
-        self.net = self.model
         self.world = dist.get_world_size() if (ddp and dist.is_initialized()) else 1
-        # data parallelism, two flavours with identical numerics (mean of the per-rank gradients):
-        #  'ddp'  : torch DistributedDataParallel (bucketed all-reduce overlapped with backward), eager launches
-        #  'flat' : one NCCL all-reduce of the flattened gradients after backward; capturable, so the whole step
-        #           (forward, backward, all-reduce, AdamW) replays as ONE CUDA graph per rank
-        self.dp_mode = None
-        if ddp:
-            self.dp_mode = 'flat' if (graph and self.device.type == 'cuda') else 'ddp'
-        if self.dp_mode == 'ddp':
-            self.net = nn.parallel.DistributedDataParallel(self.model, device_ids=[self.device.index] if self.device.type == 'cuda' else None,
-                                                           broadcast_buffers=False,
-                                                           gradient_as_bucket_view=True, bucket_cap_mb=100, static_graph=True)
-        elif self.dp_mode == 'flat':
-            with torch.no_grad():                      # same start on every rank (DDP does this broadcast itself)
+        self.params = [p for p in self.model.parameters() if p.requires_grad]
+        if self.world > 1:
+            with torch.no_grad():                      # same start on every rank
                 for p in self.model.parameters():
                     dist.broadcast(p, 0)
-        self.opt = torch.optim.AdamW([p for p in self.model.parameters() if p.requires_grad], lr=self.model.lr,
-                                     weight_decay=self.model.weight_decay, capturable=bool(graph and self.dp_mode != 'ddp'),
+        # ---- flat gradient buffer, bucketed -------------------------------------------------------------------------
+        order = self.params[::-1]
+        total = sum(p.numel() for p in order)
+        self.flat_grad = torch.zeros(total, dtype=torch.float32, device=self.device)
+        self.buckets = []                              # (start, end, parameter count)
+        nb = max(1, min(int(buckets), len(order)))
+        target, o, start, count = total / nb, 0, 0, 0
+        self._bucket_of = {}
+        for p in order:
+            p.grad = self.flat_grad[o:o + p.numel()].view_as(p)
+            self._bucket_of[p] = len(self.buckets)
+            o += p.numel(); count += 1
+            if o - start >= target and len(self.buckets) < nb - 1:
+                self.buckets.append((start, o, count)); start, count = o, 0
+        self.buckets.append((start, o, count))
+        self._pending = [c for _, _, c in self.buckets]
+        self._launched = [False] * len(self.buckets)
+        self.comm_stream = torch.cuda.Stream(self.device) if (self.world > 1 and self.device.type == 'cuda') else None
+        self.dp_mode = None
+        if self.world > 1:
+            self.dp_mode = f'flat buffer, {len(self.buckets)} buckets, all-reduce(AVG) overlapped with backward'
+            for p in order:
+                p.register_post_accumulate_grad_hook(self._grad_ready)
+        if mode == 'finetune':
+            from . import finetune
+            groups = finetune.finetune_param_groups(self.model, **ft['lrs'])
+            wd = ft['model']['weight_decay']
+        else:
+            groups, wd = [{'params': self.params, 'lr': self.model.lr}], self.model.weight_decay
+        self.opt = torch.optim.AdamW(groups, lr=self.model.lr, weight_decay=wd, capturable=bool(graph and self.device.type == 'cuda'),
                                      **(dict(fused=True) if self.device.type == 'cuda' else {}))    # one multi-tensor kernel family
         self.autocast = autocast
         self.graph = None
-        self.use_graph = bool(graph) and self.dp_mode != 'ddp' and self.device.type == 'cuda'
+        self.use_graph = bool(graph) and self.device.type == 'cuda'
         self.static = None
 
+    # ---- gradient exchange -------------------------------------------------------------------------------------------
+    def _launch_bucket(self, b):
+        start, end, _ = self.buckets[b]
+        self._launched[b] = True
+        if self.comm_stream is None:                   # CPU / gloo: same arithmetic, no overlap
+            dist.all_reduce(self.flat_grad[start:end])
+            self.flat_grad[start:end].mul_(1.0 / self.world)
+            return
+        cur = torch.cuda.current_stream(self.device)
+        self.comm_stream.wait_stream(cur)              # the bucket's gradients are complete on the compute stream
+        with torch.cuda.stream(self.comm_stream):
+            dist.all_reduce(self.flat_grad[start:end], op=dist.ReduceOp.AVG)
+
+    def _grad_ready(self, p):
+        b = self._bucket_of[p]
+        self._pending[b] -= 1
+        if self._pending[b] == 0 and not self._launched[b]:
+            self._launch_bucket(b)
+
+    def _finish_allreduce(self):
+        for b in range(len(self.buckets)):             # buckets holding a parameter that got no gradient this step
+            if not self._launched[b]:
+                self._launch_bucket(b)
+        if self.comm_stream is not None:
+            torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
+        self._pending = [c for _, _, c in self.buckets]
+        self._launched = [False] * len(self.buckets)
+
+    # ---- step --------------------------------------------------------------------------------------------------------
     def _step_eager(self, t, x, y):
-        self.opt.zero_grad(set_to_none=True)
+        self.flat_grad.zero_()                          # one memset; p.grad stay views of the flat buffer
         with torch.autocast(self.device.type, dtype=self.autocast, enabled=self.autocast is not None):
-            pred = self.net(x, t)
+            pred = self.model(x, t)
         loss = self.model.training_loss(pred.float(), y.float())
         loss.backward()
-        if self.dp_mode == 'flat':
-            self._allreduce_flat()
+        if self.world > 1:
+            self._finish_allreduce()
         self.opt.step()
         return loss.detach()
-
-    def _allreduce_flat(self):
-        grads = [p.grad for p in self.model.parameters() if p.grad is not None]
-        flat = torch.cat([g.reshape(-1) for g in grads])
-        dist.all_reduce(flat)
-        flat.mul_(1.0 / self.world)
-        torch._foreach_copy_(grads, [c.view_as(g) for c, g in zip(flat.split([g.numel() for g in grads]), grads)])
 
     def step(self, t, x, y):
         if not self.use_graph:
@@ -108,10 +160,29 @@ class Trainer:
                     self._step_eager(*self.static)
             torch.cuda.current_stream().wait_stream(s)
             self.graph = torch.cuda.CUDAGraph()
-            self.opt.zero_grad(set_to_none=True)
             with torch.cuda.graph(self.graph):
                 self.static_loss = self._step_eager(*self.static)
         for dst, src in zip(self.static, (t, x, y)):
             dst.copy_(src, non_blocking=True)
         self.graph.replay()
         return self.static_loss
+
+    def close(self):
+        """Drop the captured graph BEFORE the process group goes away: a CUDA graph that holds NCCL kernels keeps the
+        communicator's resources referenced, and destroying the communicator first blocks in its destructor."""
+        if self.device.type == 'cuda':
+            torch.cuda.synchronize(self.device)
+        self.graph = None
+        self.static = None
+        self.static_loss = None
+        if self.device.type == 'cuda':
+            torch.cuda.synchronize(self.device)
+
+
+def synthetic_finetune_batch(batch, ft, device='cuda', seed=0, dtype=torch.float32):
+    """fine-tuning sample shapes: x[B, new_in, S, S], t[B], y[B, new_out, S_out, S_out] (z-scored fields)"""
+    g = torch.Generator(device='cpu').manual_seed(seed)
+    x = torch.randn(batch, ft['in_dim'], ft['in_size'], ft['in_size'], generator=g)
+    y = torch.randn(batch, ft['out_dim'], ft['out_size'], ft['out_size'], generator=g)
+    t = torch.randint(1, 8, (batch,), generator=g).float() / 7.0
+    return t.to(device), x.to(device, dtype), y.to(device, dtype)

@@ -1,0 +1,88 @@
+"""GPU tests of the training harness: the CUDA-graph-captured step equals the eager step, the fine-tune
+workload (BASELINE.json configs[4] shape, shrunk) runs under bf16 autocast, and the captured forward-only rollout loop of
+TestCNO_ALL.py:124-188 equals the eager loop."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda'
+SMALL = dict(in_dim=7, in_size=32, N_layers=2, N_res=1, N_res_neck=2, channel_multiplier=8, out_dim=3, is_time=1, nl_dim=[2, 3],
+             latent_lift_proj_dim=16, lr=1e-3, weight_decay=1e-6)
+
+
+@pytest.fixture(scope='module')
+def cno():
+    import pregenerating_pde_b200 as pkg
+    pkg._lib.load()
+    return pkg
+
+
+def _params(tr):
+    return torch.cat([p.detach().reshape(-1) for p in tr.model.parameters()])
+
+
+def test_graph_step_equals_eager_step(cno):
+    torch.manual_seed(0)
+    a = cno.train.Trainer(SMALL, device=DEV, graph=False)
+    b = cno.train.Trainer(SMALL, device=DEV, graph=True)
+    b.model.load_state_dict(a.model.state_dict())
+    batches = [cno.train.synthetic_fpo_batch(4, size=32, device=DEV, seed=s) for s in range(3)]
+    # the graph trainer warms up with three eager steps on its first batch before capture; give the eager one the same history
+    for _ in range(3):
+        a.step(*batches[0])
+    la, lb = [], []
+    for bt in batches + batches:
+        la.append(float(a.step(*bt)))
+    for bt in [batches[0]] + batches[1:] + batches:          # first call: 3 warm-up steps + capture (no replay of the capture itself)
+        lb.append(float(b.step(*bt)))
+    # b has run 3 warm-up + 6 replays, a 3 + 6 eager steps, on the same batches in the same order
+    pa, pb = _params(a), _params(b)
+    assert torch.isfinite(pa).all() and torch.isfinite(pb).all()
+    rel = float((pa - pb).abs().max() / pa.abs().max())
+    assert rel < 2e-4, rel                                    # AdamW amplifies fp32 round-off of atomics (db) by lr / sqrt(v)
+    assert abs(la[-1] - lb[-1]) / abs(la[-1]) < 1e-3, (la, lb)
+    b.close()
+
+
+def test_finetune_step_bf16_autocast(cno):
+    ft = dict(model=dict(in_dim=5, in_size=64, N_layers=2, N_res=1, N_res_neck=1, channel_multiplier=8, out_dim=4, is_time=1, nl_dim=[2, 3],
+                         latent_lift_proj_dim=16, lr=1e-3, weight_decay=1e-6),
+              ft=dict(old_in_dim=5, new_in_dim=4, new_out_dim=4, old_out_dim=4), lrs=dict(lr=1e-3, lr_emb=1e-2, lr_norm=1e-2),
+              in_size=64, out_size=64, in_dim=4, out_dim=4)
+    tr = cno.train.Trainer(device=DEV, mode='finetune', ft=ft, autocast=torch.bfloat16, graph=True)
+    t, x, y = cno.train.synthetic_finetune_batch(4, ft, device=DEV)
+    losses = [float(tr.step(t, x, y)) for _ in range(12)]
+    assert all(l == l for l in losses) and losses[-1] < losses[0], losses      # trains: the loss on a fixed batch goes down
+    assert len(tr.opt.param_groups) == 3
+    tr.close()
+
+
+def test_rollout_graph_equals_eager(cno):
+    """forward-only autoregressive rollout (TestCNO_ALL.py:124-188: pred = model(inp, t); inp[:, :dim] = pred) captured as one
+    CUDA graph of K model calls; no sign masks are written under no_grad."""
+    torch.manual_seed(1)
+    model = cno.cno_model.CNO_time(**SMALL).to(DEV).eval()
+    t, x, _ = cno.train.synthetic_fpo_batch(2, size=32, device=DEV, seed=4)
+
+    def rollout(inp, K=4):
+        outs = []
+        inp = inp.clone()
+        for _ in range(K):
+            pred = model(inp, t)
+            inp = torch.cat([pred, inp[:, 3:]], 1)
+            outs.append(pred)
+        return torch.stack(outs)
+    with torch.no_grad():
+        ref = rollout(x)
+        s = torch.cuda.Stream(); s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            rollout(x)
+        torch.cuda.current_stream().wait_stream(s)
+        g = torch.cuda.CUDAGraph()
+        static_x = x.clone()
+        with torch.cuda.graph(g):
+            out = rollout(static_x)
+        static_x.copy_(x)
+        g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, ref)
