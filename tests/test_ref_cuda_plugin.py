@@ -65,9 +65,14 @@ def test_filtered_lrelu_vs_reference_cuda_kernel(cno, ref, name, s_in, s_out, N,
     tol = 1e-5 if dtype == torch.float32 else 2e-3
     assert rel(y_o, y_r) < tol
     assert so_o.shape == so_r.shape and so_o.dtype == so_r.dtype
-    differ = int((so_o != so_r).sum())
-    # codes can only differ where |pre-activation| is at fp32 rounding distance from 0 (different summation orders)
-    assert differ <= max(2, so_o.numel() // 200000), f'{differ} of {so_o.numel()} mask bytes differ'
+    # Codes of the real up-res columns (x < UW) must agree; they can only differ where |pre-activation| is at fp32 rounding
+    # distance from 0 (different summation orders).  The reference pads mask rows to 16 elements (filtered_lrelu.cpp:83-85) and
+    # its tiles write whatever sign they computed into those pad columns; ours writes zeros there.  No reader ever uses them
+    # (the backward kernels only index columns < UW), so pad bits are excluded from the comparison.
+    uw = s_out * down - (down - 1) + (td - 1)
+    codes = lambda m: torch.stack([(m >> (2 * i)) & 3 for i in range(4)], dim=-1).flatten(-2)[..., :uw]
+    differ = int((codes(so_o) != codes(so_r)).sum())
+    assert differ <= max(2, so_o.numel() // 50000), f'{differ} of {so_o.numel() * 4} codes differ'
     # backward: each kernel reads the OTHER implementation's mask (layout interchange both ways)
     pp = (tu + td - 2 - px0, s_in * up - s_out * down + px0 - (up - 1), tu + td - 2 - py0, s_in * up - s_out * down + py0 - (up - 1))
     gg = gain * up * up / (down * down)
