@@ -180,9 +180,15 @@ class Trainer:
 
 
 def synthetic_finetune_batch(batch, ft, device='cuda', seed=0, dtype=torch.float32):
-    """fine-tuning sample shapes: x[B, new_in, S, S], t[B], y[B, new_out, S_out, S_out] (z-scored fields)"""
+    """fine-tuning sample shapes: x[B, new_in, S, S], t[B], y[B, new_out, S_out, S_out].  Band-limited random fields (coarse
+    noise, bicubically up-sampled: the alias-free activations pass them) and a target that depends on the input (the first
+    output channels of x at the output size, mixed with the lead time), so the loss has something to learn."""
     g = torch.Generator(device='cpu').manual_seed(seed)
-    x = torch.randn(batch, ft['in_dim'], ft['in_size'], ft['in_size'], generator=g)
-    y = torch.randn(batch, ft['out_dim'], ft['out_size'], ft['out_size'], generator=g)
+    S, So = ft['in_size'], ft['out_size']
+    coarse = torch.randn(batch, ft['in_dim'], max(S // 8, 2), max(S // 8, 2), generator=g)
+    x = torch.nn.functional.interpolate(coarse, size=(S, S), mode='bicubic', align_corners=False)
     t = torch.randint(1, 8, (batch,), generator=g).float() / 7.0
-    return t.to(device), x.to(device, dtype), y.to(device, dtype)
+    src = x[:, [i % ft['in_dim'] for i in range(ft['out_dim'])]]
+    y = torch.nn.functional.interpolate(src, size=(So, So), mode='bilinear', align_corners=False, antialias=True)
+    y = y * (0.5 + t.view(-1, 1, 1, 1))
+    return t.to(device), x.contiguous().to(device, dtype), y.contiguous().to(device, dtype)

@@ -22,25 +22,36 @@ def _params(tr):
 
 
 def test_graph_step_equals_eager_step(cno):
+    """Same parameters, same batches: the captured step must produce the gradients and losses of the eager step.
+    Parameters after several AdamW steps are NOT compared element-wise: convolution biases in front of an instance norm have
+    a mathematically zero gradient, so their computed gradient is fp32 round-off (and the order of the db atomics), which
+    AdamW's m / sqrt(v) turns into +-lr steps of arbitrary sign.  Gradients are compared with the optimiser frozen (lr = 0),
+    the training trajectory through its losses."""
+    torch.manual_seed(0)
+    cfg0 = dict(SMALL, lr=0.0, weight_decay=0.0)
+    a = cno.train.Trainer(cfg0, device=DEV, graph=False)
+    b = cno.train.Trainer(cfg0, device=DEV, graph=True)
+    b.model.load_state_dict(a.model.state_dict())
+    batches = [cno.train.synthetic_fpo_batch(4, size=32, device=DEV, seed=s) for s in range(3)]
+    for bt in batches + batches:
+        la, ga = float(a.step(*bt)), a.flat_grad.clone()
+        lb, gb = float(b.step(*bt)), b.flat_grad.clone()
+        assert torch.isfinite(gb).all()
+        assert abs(la - lb) <= 1e-5 * abs(la), (la, lb)
+        # fp32 floor: the db atomics and cuDNN's algorithm choice may differ between the warm-up and the captured launches
+        assert float((ga - gb).abs().max() / ga.abs().max()) < 1e-4
+    b.close()
+    # with the optimiser running: same loss trajectory (3 warm-up steps precede the capture, give the eager trainer the same history)
     torch.manual_seed(0)
     a = cno.train.Trainer(SMALL, device=DEV, graph=False)
     b = cno.train.Trainer(SMALL, device=DEV, graph=True)
     b.model.load_state_dict(a.model.state_dict())
-    batches = [cno.train.synthetic_fpo_batch(4, size=32, device=DEV, seed=s) for s in range(3)]
-    # the graph trainer warms up with three eager steps on its first batch before capture; give the eager one the same history
     for _ in range(3):
         a.step(*batches[0])
-    la, lb = [], []
-    for bt in batches + batches:
-        la.append(float(a.step(*bt)))
-    for bt in [batches[0]] + batches[1:] + batches:          # first call: 3 warm-up steps + capture (no replay of the capture itself)
-        lb.append(float(b.step(*bt)))
-    # b has run 3 warm-up + 6 replays, a 3 + 6 eager steps, on the same batches in the same order
-    pa, pb = _params(a), _params(b)
-    assert torch.isfinite(pa).all() and torch.isfinite(pb).all()
-    rel = float((pa - pb).abs().max() / pa.abs().max())
-    assert rel < 2e-4, rel                                    # AdamW amplifies fp32 round-off of atomics (db) by lr / sqrt(v)
-    assert abs(la[-1] - lb[-1]) / abs(la[-1]) < 1e-3, (la, lb)
+    la = [float(a.step(*bt)) for bt in batches + batches]
+    lb = [float(b.step(*bt)) for bt in batches + batches]
+    assert all(abs(x - y) / abs(x) < 1e-3 for x, y in zip(la, lb)), (la, lb)
+    assert torch.isfinite(_params(b)).all()
     b.close()
 
 
@@ -51,8 +62,8 @@ def test_finetune_step_bf16_autocast(cno):
               in_size=64, out_size=64, in_dim=4, out_dim=4)
     tr = cno.train.Trainer(device=DEV, mode='finetune', ft=ft, autocast=torch.bfloat16, graph=True)
     t, x, y = cno.train.synthetic_finetune_batch(4, ft, device=DEV)
-    losses = [float(tr.step(t, x, y)) for _ in range(12)]
-    assert all(l == l for l in losses) and losses[-1] < losses[0], losses      # trains: the loss on a fixed batch goes down
+    losses = [float(tr.step(t, x, y)) for _ in range(30)]
+    assert all(l == l for l in losses) and min(losses[-5:]) < 0.9 * losses[0], losses      # trains: the loss on a fixed batch goes down
     assert len(tr.opt.param_groups) == 3
     tr.close()
 
