@@ -71,6 +71,13 @@ int cno_filtered_lrelu(const void* x, void* y, const void* b, uint8_t* mask, flo
 int cno_filtered_lrelu_query(int dtype, int in_h, int in_w, int out_h, int out_w, int fu_taps,
                              int fd_taps, int up, int down, int px0, int py0);
 
+/* The fused op has two kernels behind cno_filtered_lrelu: a streaming kernel (TMA row strips, four up-res columns per thread) and,
+ * for up-res planes of at most 64 columns, a whole-plane kernel (planes resident in shared memory, one thread per column).  The
+ * reference picks among its tile specialisations the same way (filtered_lrelu.cu:1240-1270 spec table); results are identical up
+ * to fp32 summation order.  enable = 1 / 0 switches the whole-plane kernel on / off (default on; environment CNO_FLR_NO_PLANE
+ * turns it off), enable < 0 only queries; returns the previous setting.  Used by the tests to run both kernels on the same data. */
+int cno_filtered_lrelu_plane_kernel(int enable);
+
 /* replaces _plugin.filtered_lrelu_act_(x, si, sx, sy, gain, slope, clamp, write_signs)
  * (filtered_lrelu.cpp:205-282, kernel filtered_lrelu.cu:1097-1203): in-place gain*lrelu, clamp on a
  * dense [planes,h,w] tensor with 2-bit mask write / read.  Generic-fallback only. */

@@ -17,6 +17,7 @@ SIGNATURES = {
     'cno_upfirdn2d': (_I, [_P, _P, _P, _I, _I, _L] + [_I] * 13 + [_F, _P]),
     'cno_filtered_lrelu': (_I, [_P] * 7 + [_I] * 19 + [_F, _F, _F, _I, _P]),
     'cno_filtered_lrelu_query': (_I, [_I] * 11),
+    'cno_filtered_lrelu_plane_kernel': (_I, [_I]),
     'cno_filtered_lrelu_act': (_I, [_P, _P, _I, _L] + [_I] * 8 + [_F, _F, _F, _P]),
     'cno_cin_fwd': (_I, [_P] * 8 + [_I] * 4 + [_F, _P]),
     'cno_cin_bwd': (_I, [_P] * 9 + [_I] * 4 + [_P]),

@@ -12,7 +12,8 @@ CSRC = os.path.join(HERE, 'csrc')
 OBJ = os.path.join(os.path.dirname(HERE), 'build', 'cno_b200')
 LIB = os.path.join(HERE, 'libcno_b200.so')
 SOURCES = ['capi.cu', 'bias_act.cu', 'upfirdn2d.cu', 'flrelu_act.cu', 'cin.cu', 'flrelu_fused.cu',
-           'flrelu_fused_f32.cu', 'flrelu_fused_bf16.cu', 'flrelu_fused_f16.cu']
+           'flrelu_fused_f32.cu', 'flrelu_fused_bf16.cu', 'flrelu_fused_f16.cu',
+           'flrelu_plane_f32.cu', 'flrelu_plane_bf16.cu', 'flrelu_plane_f16.cu']
 NVCC_FLAGS = ['-std=c++17', '-O3', '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo',
               '-Xcompiler', '-fPIC', '--threads', '2']
 

@@ -9,7 +9,7 @@ import os
 import torch
 
 from . import _lib
-from .torch_utils.custom_ops import _DT, _ptr, _stream
+from .torch_utils.custom_ops import _DT, _ptr, _stream, profiled as _profiled
 
 
 FUSE_LRELU = os.environ.get('CNO_FUSE_LRELU', '1') != '0'         # False: film_lrelu runs FILM and the activation as two ops (the normalised tensor goes through HBM)
@@ -196,6 +196,7 @@ def _film_fusable(self, x):
             and all(m.weight.dtype == torch.float32 for m in lin))
 
 
+@_profiled('cno::film')
 def film_forward(self, x, timestep, residual=None):
     """Replacement for FILM.forward (CNO_timeModule_CIN.py:60-70).  Uses the fused kernel when the module
     is the instance-norm flavour on a CUDA tensor; every other case runs the module's own torch ops.
@@ -224,6 +225,7 @@ def _film_kernel_ok(self, x, timestep):
             and FUSE_LINEARS and _film_fusable(self, x) and not timestep.requires_grad)
 
 
+@_profiled('cno::film_lrelu')
 def film_lrelu(film, act, x, timestep):
     """act(film(x, timestep)) for a FILM module followed by an LReLu module (CNOBlock.forward, CNO_timeModule_CIN.py:329-335;
     ResidualBlock.forward :499-500).  When both have a fused kernel the normalised tensor is never written: one statistics pass

@@ -16,6 +16,7 @@ import numpy as np
 import scipy.signal
 import scipy.special
 import torch
+import torch.nn.functional as F
 from torch import nn
 
 from .torch_utils.ops import filtered_lrelu
@@ -73,6 +74,38 @@ class LReLu(nn.Module):
         return y
 
 
+class LReLu_torch(nn.Module):
+    """The reference's torch-only activation (training/filtered_networks.py:349-388, `activation='cno_lrelu_torch'` of
+    CNOBlock / ResidualBlock, CNO_timeModule_CIN.py:299-305, :461-467): bicubic antialiased interpolation to 2x, LeakyReLU
+    (default slope 0.01), back to the input size, on to the output size, bias added last.  Plain torch ops (no kernel of this
+    package is involved); kept so that checkpoints and configurations that select it load and run."""
+
+    def __init__(self, in_channels, out_channels, in_size, out_size, in_sampling_rate=None, out_sampling_rate=None):
+        super().__init__()
+        assert in_channels == out_channels
+        self.activation = nn.LeakyReLU()
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.in_size, self.out_size = in_size, out_size
+        self.in_sampling_rate, self.out_sampling_rate = in_sampling_rate, out_sampling_rate
+        self.bias = nn.Parameter(torch.zeros([out_channels]))
+
+    def forward(self, x):
+        x = F.interpolate(x, size=2 * self.in_size, mode='bicubic', antialias=True)
+        x = self.activation(x)
+        x = F.interpolate(x, size=self.in_size, mode='bicubic', antialias=True)
+        x = F.interpolate(x, size=self.out_size, mode='bicubic', antialias=True)
+        return x + self.bias.view(1, -1, 1, 1)
+
+
+def _make_activation(kind, channels, in_size, out_size, cutoff_den, half_width_mult, filter_size, lrelu_upsampling, impl):
+    if kind == 'cno_lrelu':
+        return LReLu(channels, channels, in_size, out_size, filter_size=filter_size, lrelu_upsampling=lrelu_upsampling,
+                     is_critically_sampled=(cutoff_den == 2.0), impl=impl, **_filter_args(in_size, out_size, cutoff_den, half_width_mult))
+    if kind == 'cno_lrelu_torch':
+        return LReLu_torch(channels, channels, in_size, out_size, in_size, out_size)
+    raise ValueError('Please specify different activation function')      # CNO_timeModule_CIN.py:315
+
+
 class FILM(nn.Module):
     """Time-conditioned instance norm (CNO_timeModule_CIN.py:27-70); forward = the fused CIN kernel."""
 
@@ -102,14 +135,13 @@ class CNOBlock(nn.Module):
     """conv3x3 -> (CIN) -> LReLu; D / U / I by the in/out sizes (CNO_timeModule_CIN.py:227-335)."""
 
     def __init__(self, in_channels, out_channels, in_size, out_size, cutoff_den=2.0001, conv_kernel=3, filter_size=6,
-                 lrelu_upsampling=2, half_width_mult=0.8, is_time=True, nl_dim=(2, 3), impl='cuda'):
+                 lrelu_upsampling=2, half_width_mult=0.8, is_time=True, nl_dim=(2, 3), impl='cuda', activation='cno_lrelu'):
         super().__init__()
         self.in_channels, self.out_channels, self.in_size, self.out_size = in_channels, out_channels, in_size, out_size
         self.convolution = nn.Conv2d(in_channels, out_channels, conv_kernel, padding=(conv_kernel - 1) // 2)
         self.batch_norm = nn.Identity()
-        self.activation = LReLu(out_channels, out_channels, in_size, out_size, filter_size=filter_size,
-                                lrelu_upsampling=lrelu_upsampling, is_critically_sampled=(cutoff_den == 2.0), impl=impl,
-                                **_filter_args(in_size, out_size, cutoff_den, half_width_mult))
+        self.activation = _make_activation(activation, out_channels, in_size, out_size, cutoff_den, half_width_mult, filter_size,
+                                           lrelu_upsampling, impl)
         self.is_time = bool(is_time)
         if self.is_time:
             self.in_norm_conditiner = FILM(out_channels, dim=nl_dim, s=in_size)
@@ -138,15 +170,14 @@ class ResidualBlock(nn.Module):
     """x + CIN(conv(LReLu(CIN(conv(x))))) (CNO_timeModule_CIN.py:393-510)."""
 
     def __init__(self, channels, size, cutoff_den=2.0001, conv_kernel=3, filter_size=6, lrelu_upsampling=2,
-                 half_width_mult=0.8, is_time=True, nl_dim=(2, 3), impl='cuda'):
+                 half_width_mult=0.8, is_time=True, nl_dim=(2, 3), impl='cuda', activation='cno_lrelu'):
         super().__init__()
         self.channels, self.size = channels, size
         pad = (conv_kernel - 1) // 2
         self.convolution1 = nn.Conv2d(channels, channels, conv_kernel, stride=1, padding=pad)
         self.convolution2 = nn.Conv2d(channels, channels, conv_kernel, stride=1, padding=pad)
         self.batch_norm1, self.batch_norm2 = nn.Identity(), nn.Identity()
-        self.activation = LReLu(channels, channels, size, size, filter_size=filter_size, lrelu_upsampling=lrelu_upsampling,
-                                is_critically_sampled=(cutoff_den == 2.0), impl=impl, **_filter_args(size, size, cutoff_den, half_width_mult))
+        self.activation = _make_activation(activation, channels, size, size, cutoff_den, half_width_mult, filter_size, lrelu_upsampling, impl)
         self.is_time = bool(is_time)
         if self.is_time:
             self.in_norm_conditiner1 = FILM(channels, dim=nl_dim, s=size)
@@ -170,7 +201,7 @@ class CNO_time(nn.Module):
     def __init__(self, in_dim, in_size, N_layers, N_res=1, N_res_neck=6, channel_multiplier=32, conv_kernel=3,
                  cutoff_den=2.0001, filter_size=6, lrelu_upsampling=2, half_width_mult=0.8, out_dim=1,
                  latent_lift_proj_dim=64, add_inv=True, is_time=1, nl_dim=(2, 3), lr=0.0005, weight_decay=1e-6, impl='cuda',
-                 project_out_size=None):
+                 project_out_size=None, activation='cno_lrelu'):
         super().__init__()
         self.N_layers, self.N_res, self.N_res_neck = int(N_layers), int(N_res), int(N_res_neck)
         self.in_dim, self.out_dim, self.add_inv = in_dim, out_dim, add_inv
@@ -186,7 +217,7 @@ class CNO_time(nn.Module):
         self.encoder_sizes = [in_size // 2 ** i for i in range(L + 1)]
         self.decoder_sizes = [in_size // 2 ** (L - i) for i in range(L + 1)]
         kw = dict(cutoff_den=cutoff_den, conv_kernel=conv_kernel, filter_size=filter_size, lrelu_upsampling=lrelu_upsampling,
-                  half_width_mult=half_width_mult, impl=impl)
+                  half_width_mult=half_width_mult, impl=impl, activation=activation)     # 'cno_lrelu' | 'cno_lrelu_torch' (:534)
         tkw = dict(kw, is_time=is_time, nl_dim=nl_dim)
         es, ds = self.encoder_sizes, self.decoder_sizes
         self.lift = LiftProjectBlock(in_dim, enc[0], in_size, es[0], latent_dim=latent_lift_proj_dim, **kw)

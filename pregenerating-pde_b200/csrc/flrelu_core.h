@@ -101,6 +101,9 @@ template <> struct Cvt<float> { static FLR_DEV float get(float v) { return v; } 
 #endif
 constexpr int NSTAGE = FLR_NSTAGE;
 constexpr int NDBUF = 3;           // D buffers (finished v-down rows) in flight, see flr_fused_kernel
+constexpr int MSP = FLR_MAXT;      // WRITE: row pitch of the staged sign bytes, layout [up-res row of the body][thread]: a thread's
+                                   // byte of row jl sits at the compile-time offset jl * MSP from its own slot (one STS.U8, no
+                                   // address arithmetic); mask_out() copies finished bodies to HBM with 32-bit stores
 
 // Everything the kernel needs besides the tensor map.  Filled by the host (flrelu_fused.cu).
 struct Params {
@@ -126,8 +129,10 @@ struct Params {
                                // writers (consecutive f) and the h-down readers (f = DOWN*cq + i) are both bank-conflict free and
                                // a reader's NF4 loads are constant offsets from one address
     int ncq, ncq_shift;        // output column quads per row = ceil(OW/4); log2 when a power of two, else -1
+    int hstep;                 // h-down: row lanes per plane slot = min(G / ncq, KO) (hdown_phase)
     int stage_bytes;           // bytes of one x stage (multiple of 128)
     int mask_h, mask_w, mask_pitch, sx, sy;
+    int mlanes;                // READ: row lanes of stage_mask per plane slot = G / mnw (>= 1)
     int mws, mnw, mstride;     // READ: staged mask window per row: first byte (multiple of 4, may be < 0), 32-bit words, smem row stride
     float slope;
 };
@@ -204,7 +209,11 @@ struct Stream {
     bool active;
     uint32_t colmask;       // WRITE: valid-column bits; READ: valid mask-element bits
     int rd_word, rd_bits;   // READ: 32-bit word of the staged mask row that holds this thread's first code bit, and its bit position
-    uint8_t* mrow0;         // mask row 0 of this thread's plane (+ group byte for WRITE)
+    int sm_dst, sm_lane;    // READ: stage_mask role of this thread inside its plane slot: byte offset of its word column in the staged rows
+                            // of the unit, first row it copies (rows sm_lane, sm_lane + mlanes, ...; >= PB: no role)
+    const uint8_t* sm_src;  // READ: that word column in row 0 of the plane's mask (nullptr: outside the mask, zero-fill)
+    int mo_src;             // WRITE: byte offset of this thread's first staged word inside a staging buffer (mask_out): jl0 * MSP + unit * G + 4 * wc
+    uint8_t* mo_dst;        // WRITE: that word's place in the mask of the thread's plane, row jl0 of up-res row 0
     // fused db = y.sum([0,2,3]): sum over the outputs of a row = dot(finished v-down row, column weights), the weight of
     // column c being the sum of the down taps through which c reaches a valid output column
     f2 dbw[2], dbacc[2];
@@ -224,7 +233,7 @@ struct Stream {
         FLR_UNROLL for (int r = 0; r < C::ND; r++) { acc[r][0] = mk2(0.f, 0.f); acc[r][1] = mk2(0.f, 0.f); }
         FLR_UNROLL for (int w = 0; w < C::WLY; w++) { win[w][0] = mk2(0.f, 0.f); win[w][1] = mk2(0.f, 0.f); }
         bE[0] = bE[1] = mk2(0.f, 0.f);
-        colmask = 0; rd_word = 0; rd_bits = 0; mrow0 = nullptr;
+        colmask = 0; rd_word = 0; rd_bits = 0; mo_src = 0; mo_dst = nullptr; sm_dst = 0; sm_lane = C::PB; sm_src = nullptr;
         dbw[0] = dbw[1] = dbacc[0] = dbacc[1] = mk2(0.f, 0.f); db_lo = db_hi = 0; aff2 = mk2(1.f, 1.f);
         if (!active) return;
         if (FLR_IS_READ(MODE) && p.db) {       // db is a backward quantity: only the mask-reading variant carries the code
@@ -254,23 +263,35 @@ struct Stream {
         }
         if (MODE == SIGN_WRITE) {
             FLR_UNROLL for (int m = 0; m < 4; m++) if (4 * g + m < p.UW) colmask |= 1u << (2 * m);   // bit 0 of each 2-bit code
-            mrow0 = p.mask + (int64_t)plane * p.mask_h * p.mask_pitch + g;
+            {   // mask_out role: G/4 word columns x 4 row lanes per plane slot
+                const int nwr = p.G >> 2, jl0 = g / nwr, wc = g - jl0 * nwr;
+                mo_src = jl0 * MSP + unit * p.G + 4 * wc;
+                mo_dst = p.mask + ((int64_t)plane * p.mask_h + jl0) * p.mask_pitch + 4 * wc;
+            }
         } else if (FLR_IS_READ(MODE)) {
             const int e0 = 4 * g + p.sx;
             const int fl = (e0 >= 0) ? e0 / 4 : -((-e0 + 3) / 4);
             rd_word = (fl - p.mws) >> 2; rd_bits = 8 * ((fl - p.mws) & 3) + 2 * (e0 - 4 * fl);     // fl >= mws by construction (set_mask_window)
             FLR_UNROLL for (int m = 0; m < 4; m++) { const int e = e0 + m; if (e >= 0 && e < p.mask_w) colmask |= 3u << (2 * m); }
-            mrow0 = p.mask + (int64_t)plane * p.mask_h * p.mask_pitch;
+            {   // stage_mask role: mnw word columns x mlanes row lanes per plane slot
+                const int lane = g / p.mnw, wc = g - lane * p.mnw, byte = p.mws + 4 * wc;
+                sm_lane = lane < p.mlanes ? lane : C::PB;
+                sm_dst = unit * C::PB * p.mstride + 4 * wc;
+                sm_src = (byte >= 0 && byte < p.mask_pitch) ? p.mask + (int64_t)plane * p.mask_h * p.mask_pitch + byte : nullptr;
+            }
         }
     }
 
     // horizontal polyphase up-FIR of one staged input row -> two column pairs
+    //   XPAR : parity of xshift when the caller knows it at compile time (0 / 1; the streaming body is instantiated for both so
+    //          that its rows form one basic block), -1 = test p.xshift (prologue)
+    template <int XPAR = -1>
     FLR_DEV void hup(const Params& p, const T* xrow /* tile row of this unit */, bool rowvalid, f2 out[2]) {
         float xs[8];
         const int xoff = xofs;
 #if defined(__CUDA_ARCH__)
         if (C::UP == 2 && sizeof(T) == 4) {          // LDS.64 from the even column at or below xoff
-            if (p.xshift & 1) {                      // uniform branch (the parity of xofs is that of xshift: 2g and bstep are even): LDS.32, 3 x LDS.64, LDS.32
+            if (XPAR < 0 ? (p.xshift & 1) : XPAR) {  // uniform (the parity of xofs is that of xshift: 2g and bstep are even): LDS.32, 3 x LDS.64, LDS.32
                 xs[0] = xrow[xoff];
                 FLR_UNROLL for (int w = 0; w < 3; w++) { const float2 v = *reinterpret_cast<const float2*>(xrow + xoff + 1 + 2 * w); xs[1 + 2 * w] = v.x; xs[2 + 2 * w] = v.y; }
                 xs[7] = xrow[xoff + 7];
@@ -345,13 +366,16 @@ struct Stream {
     //   jb    : global up-res row index of the body's first row
     //   Dbuf  : this unit's KO x dp floats of the D buffer being filled
     //   Mrows : READ: this unit's PB staged mask rows of the body
-    FLR_DEV void body(const Params& p, const T* xtile, int grow0, int jb, float* Dbuf, const uint8_t* Mrows) {
+    //   Mst   : WRITE: this thread's byte of row 0 in the staging buffer of the body (rows MSP apart)
+    //   EDGE  : false = the caller guarantees that every input row of the body lies inside the plane (no row-validity selects)
+    template <bool EDGE, int XPAR>
+    FLR_DEV void body(const Params& p, const T* xtile, int grow0, int jb, float* Dbuf, const uint8_t* Mrows, uint8_t* Mst) {
         FLR_UNROLL for (int jl = 0; jl < C::PB; jl++) {
             const int phi = jl % C::UP, qq = jl / C::UP;
             if (phi == 0) {
                 const int grow = grow0 + qq;
                 f2 a[2];
-                hup(p, xtile + qq * p.bwx, grow >= 0 && grow < p.H, a);
+                this->template hup<XPAR>(p, xtile + qq * p.bwx, EDGE ? (grow >= 0 && grow < p.H) : true, a);
                 push(a);
             }
             const int j = jb + jl;
@@ -365,12 +389,8 @@ struct Stream {
                 v[1] = ffma2(win[(phi > C::RY ? 1 : 0) + k][1], t, v[1]);
             }
             act(p, v, code);
-#ifndef FLR_X_NOMASK
-            // 32-bit row offset (uniform across the CTA: one UIMAD, no per-thread 64-bit address arithmetic)
-            if (MODE == SIGN_WRITE) { if (j < p.UH) mrow0[(uint32_t)(j * p.mask_pitch)] = (uint8_t)code; }
-#else
-            if (MODE == SIGN_WRITE) { if (j < p.UH && code == 0x12345u) mrow0[(int64_t)j * p.mask_pitch] = (uint8_t)code; }
-#endif
+            if (MODE == SIGN_WRITE) Mst[jl * MSP] = (uint8_t)code;      // staged; rows beyond UH are dropped by mask_out()
+            (void)j;
             // vertical down-FIR, scatter form: row r of this body completes at jl = DOWN*r + DOWN-1
             FLR_UNROLL for (int r = 0; r < C::ND; r++) {
                 const int t = (jl <= C::DOWN * r + C::DOWN - 1) ? jl + C::DOWN * (C::ND - 1 - r) : jl - C::DOWN * (r + 1);
@@ -406,41 +426,55 @@ struct Stream {
 // copy4(dst, src, ok) moves one aligned 32-bit word (cp.async on the device) or zero-fills when !ok.
 // ------------------------------------------------------------------------------------------------
 template <class C, class CP>
-FLR_DEV void stage_mask(const Params& p, const CtaGeom& cg, int jb, int tid, int nthreads, uint8_t* Mdst, CP copy4) {
-    // a thread owns one 32-bit word column (plane slot u, word i) and walks down the PB rows of the body: the plane / column
-    // bounds and the address are set up once, each row then costs a row-bound predicate, one pointer step and the copy
-    for (int task = tid; task < p.P * p.mnw; task += nthreads) {
-        const int u = task / p.mnw, i = task - u * p.mnw;
-        const int plane = cg.plane0 + u, byte = p.mws + 4 * i, my0 = jb + p.sy;
-        const bool cok = plane < p.NC && byte >= 0 && byte < p.mask_pitch;
-        const int64_t off0 = cok ? ((int64_t)plane * p.mask_h + my0) * p.mask_pitch + byte : 0;
-        uint8_t* dst = Mdst + (size_t)u * C::PB * p.mstride + 4 * i;
-        const uint8_t* src = p.mask + off0;
-        FLR_NOUNROLL for (int jl = 0; jl < C::PB; jl++) {     // rolled: the copies are asynchronous, unrolling only costs registers
-            const bool ok = cok && my0 + jl >= 0 && my0 + jl < p.mask_h;
-            copy4(dst, ok ? src : p.mask, ok);
-            dst += p.mstride; src += p.mask_pitch;
-        }
+FLR_DEV void stage_mask(const Params& p, int sm_lane, int sm_dst, const uint8_t* sm_src, int jb, uint8_t* Mdst, CP copy4) {
+    // the G threads of a plane slot stage their own plane: a thread owns one 32-bit word column and every mlanes-th row of the body
+    const int my0 = jb + p.sy;
+    for (int jl = sm_lane; jl < C::PB; jl += p.mlanes) {
+        const int row = my0 + jl;
+        const bool ok = sm_src != nullptr && row >= 0 && row < p.mask_h;
+        copy4(Mdst + sm_dst + jl * p.mstride, ok ? sm_src + (int64_t)row * p.mask_pitch : p.mask, ok);
     }
 }
 
 // ------------------------------------------------------------------------------------------------
-// horizontal down-FIR of the finished rows of one body; writes y.  Called by every thread.
+// WRITE mode: copy the staged sign bytes of one finished body (layout [PB rows][MSP], thread t's byte at column t, i.e. plane
+// slot u occupies bytes [u*G, u*G + G) of every row) to the mask in HBM with 32-bit words.  The G threads of a plane slot
+// copy their own plane: G/4 word columns x 4 row lanes, a thread takes rows jl0, jl0 + 4, ... (immediate offsets in shared
+// memory, one pointer step per row in HBM).  G is a multiple of 4 and the host checks mask_pitch % 4 == 0: all words aligned.
+// ------------------------------------------------------------------------------------------------
+template <class C>
+FLR_DEV void mask_out(const Params& p, int mo_src, uint8_t* mo_dst, int jb, const uint8_t* Mbuf) {
+    const int jl0 = mo_src / MSP;                           // MSP is a power of two
+    int rows = p.UH - jb; if (rows > C::PB) rows = C::PB;
+    const uint8_t* src = Mbuf + mo_src;
+    uint32_t w[C::PB / 4];
+    FLR_UNROLL for (int it = 0; it < C::PB / 4; it++) w[it] = *reinterpret_cast<const uint32_t*>(src + 4 * it * MSP);
+    uint8_t* dst = mo_dst + (uint32_t)(jb * p.mask_pitch);
+    FLR_UNROLL for (int it = 0; it < C::PB / 4; it++) {
+        if (jl0 + 4 * it < rows) *reinterpret_cast<uint32_t*>(dst) = w[it];
+        dst += 4 * p.mask_pitch;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// horizontal down-FIR of the finished rows of one body; writes y.  The G threads of a plane slot process their own plane:
+// thread g takes output column quad g % ncq and the rows g / ncq, g / ncq + hstep, ... of the KO finished rows
+// (hstep = min(G / ncq, KO) row lanes, set by the host; G >= DOWN * ncq, so there are at least DOWN lanes).  No task index has to
+// be decomposed per output and only D rows written by the plane's own threads are read.
 // ------------------------------------------------------------------------------------------------
 template <class T, class C, class ST>
-FLR_DEV void hdown_phase(const Params& p, const CtaGeom& cg, int tid, int nthreads, int body_idx,
-                         const float* Dbuf /* [P][KO][dp] */, ST store4) {
+FLR_DEV void hdown_phase(const Params& p, const CtaGeom& cg, int plane, int unit, int g, int body_idx,
+                         const float* Dunit /* this plane slot's [KO][dp] */, ST store4) {
+    int r, cq;
+    if (p.ncq_shift >= 0) { cq = g & (p.ncq - 1); r = g >> p.ncq_shift; }
+    else { r = g / p.ncq; cq = g - r * p.ncq; }
+    if (r >= p.hstep) return;
     const int o_base = cg.o0 - (C::ND - 1) + body_idx * C::KO;
-    const int ntask = p.P * C::KO * p.ncq;
     const unsigned nrows_ok = (unsigned)(cg.o1 - cg.o0);
-    for (int task = tid; task < ntask; task += nthreads) {
-        int cq, t2;                                            // t2 = unit * KO + row: D rows are contiguous in that order
-        if (p.ncq_shift >= 0) { cq = task & (p.ncq - 1); t2 = task >> p.ncq_shift; }
-        else { t2 = task / p.ncq; cq = task - t2 * p.ncq; }
-        const int u = t2 / C::KO, r = t2 - u * C::KO;
-        const int o = o_base + r, plane = cg.plane0 + u;
-        if ((unsigned)(o - cg.o0) >= nrows_ok || plane >= p.NC) continue;
-        const f4* drow = reinterpret_cast<const f4*>(Dbuf + t2 * p.dp) + cq;
+    for (; r < C::KO; r += p.hstep) {
+        const int o = o_base + r;
+        if ((unsigned)(o - cg.o0) >= nrows_ok) continue;
+        const f4* drow = reinterpret_cast<const f4*>(Dunit + r * p.dp) + cq;
         f4 d[C::NF4];
         FLR_UNROLL for (int i = 0; i < C::NF4; i++) d[i] = drow[(i / C::DOWN) + (i % C::DOWN) * p.dq];
         float out[4];

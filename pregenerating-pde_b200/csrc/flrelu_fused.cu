@@ -1,14 +1,30 @@
 // C entry points of the fused filtered_lrelu kernel (kernels are instantiated per dtype in
 // flrelu_fused_{f32,bf16,f16}.cu so the translation units build in parallel).
 #include "flrelu_fused_impl.cuh"
+#include "flrelu_plane.cuh"
 
 namespace flr_impl {
 extern template int launch_cfg<float>(const Plan&, const CUtensorMap&, int, cudaStream_t);
 extern template int launch_cfg<__nv_bfloat16>(const Plan&, const CUtensorMap&, int, cudaStream_t);
 extern template int launch_cfg<__half>(const Plan&, const CUtensorMap&, int, cudaStream_t);
 }
+namespace flr_plane {
+extern template int launch_cfg<float>(const Plan&, const Geom&, const void*, int, cudaStream_t);
+extern template int launch_cfg<__nv_bfloat16>(const Plan&, const Geom&, const void*, int, cudaStream_t);
+extern template int launch_cfg<__half>(const Plan&, const Geom&, const void*, int, cudaStream_t);
+}
 using namespace flr;
 using namespace flr_impl;
+
+// small planes take the whole-plane kernel (flrelu_plane.cuh) unless it is switched off: environment CNO_FLR_NO_PLANE at first use,
+// or cno_filtered_lrelu_plane_kernel(0) (tests run both kernels on the same inputs)
+static EnvFlag g_no_plane;
+static std::atomic<int> g_plane_switch{-1};      // -1: follow the environment
+extern "C" int cno_filtered_lrelu_plane_kernel(int enable) {
+    const int prev = g_plane_switch.load() < 0 ? (g_no_plane.on("CNO_FLR_NO_PLANE") ? 0 : 1) : g_plane_switch.load();
+    if (enable >= 0) g_plane_switch.store(enable ? 1 : 0);
+    return prev;
+}
 
 
 extern "C" int cno_filtered_lrelu_query(int dtype, int in_h, int in_w, int out_h, int out_w, int fu_taps,
@@ -65,12 +81,27 @@ extern "C" int cno_filtered_lrelu_affine(const void* x, void* y, const void* b, 
         CNO_CHECK_ARG(mask_h >= p.UH && mask_pitch >= p.G, "filtered_lrelu: mask [%d rows x %d bytes] smaller than [%d x %d]", mask_h, mask_pitch, p.UH, p.G);
     p.y = y; p.b = b; p.mask = mask; p.db = db; p.pa = aff_a; p.pd = aff_d;
     if (aff_a && (sign_mode == CNO_SIGN_READ || sign_mode == CNO_SIGN_READ_SIGNONLY)) return -1;   // the affine belongs to the forward
-    if (reading) {
-        if (((uintptr_t)mask & 3u) || (mask_pitch & 3)) return -1;     // staged with aligned 32-bit copies
-        set_mask_window(plan, sx);
+    if (reading || sign_mode == CNO_SIGN_WRITE) {
+        if (((uintptr_t)mask & 3u) || (mask_pitch & 3)) return -1;     // staged through shared memory with aligned 32-bit copies
+        if (reading) set_mask_window(plan, sx);
     }
     p.mask_h = mask_h; p.mask_w = mask_w; p.mask_pitch = mask_pitch; p.sx = sx; p.sy = sy;
 
+    cudaStream_t st = (cudaStream_t)stream;
+    {   // small planes: whole planes in shared memory, one thread per up-res column (flrelu_plane.cuh)
+        flr_plane::Geom g;
+        if (cno_filtered_lrelu_plane_kernel(-1) && flr_plane::make_geom(g, plan) == 0) {
+            g.mb0 = p.mws;
+            switch (dtype) {
+                case CNO_F32: return flr_plane::launch_cfg<float>(plan, g, x, sign_mode, st);
+#ifndef FLR_QUICK
+                case CNO_BF16: return flr_plane::launch_cfg<__nv_bfloat16>(plan, g, x, sign_mode, st);
+                case CNO_F16: return flr_plane::launch_cfg<__half>(plan, g, x, sign_mode, st);
+#endif
+            }
+            return -1;
+        }
+    }
     EncodeTiledFn enc = get_encode();
     if (!enc) { cno_set_error("filtered_lrelu: cuTensorMapEncodeTiled not available from the driver"); return (int)cudaErrorNotSupported; }
     CUtensorMap map;
@@ -83,7 +114,6 @@ extern "C" int cno_filtered_lrelu_affine(const void* x, void* y, const void* b, 
     CUresult r = enc(&map, dt, 3, const_cast<void*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                      CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { cno_set_error("filtered_lrelu: cuTensorMapEncodeTiled failed (%d)", (int)r); return (int)cudaErrorInvalidValue; }
-    cudaStream_t st = (cudaStream_t)stream;
     switch (dtype) {
         case CNO_F32: return launch_cfg<float>(plan, map, sign_mode, st);
 #ifndef FLR_QUICK

@@ -17,6 +17,13 @@ template <> struct Cvt<__half> { static __device__ __forceinline__ float get(__h
 namespace flr_impl {
 using namespace flr;
 
+#ifdef FLR_TIMING     // diagnostic builds (tools/variants.sh): per-warp cycle accounting of the streaming loop, read by cno_flr_prof_read()
+static __device__ long long g_flr_prof[148 * 16 * 8];
+#define FLR_T(i) { const long long t_ = clock64(); tacc[i] += t_ - tlast; tlast = t_; }
+#else
+#define FLR_T(i)
+#endif
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
@@ -25,6 +32,7 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    // (a suspend-time hint on try_wait was measured twice, rounds 1 and 2: the poll rate and the launch time do not change)
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "WAIT_%=:\n\t"
@@ -73,8 +81,9 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     const size_t dbuf = (size_t)p.P * C::KO * p.dp;                      // floats per D buffer
     uint64_t* bars = reinterpret_cast<uint64_t*>(D + NDBUF * dbuf);
     uint64_t* full = bars + NSTAGE;
-    uint8_t* M = reinterpret_cast<uint8_t*>(bars) + 64;                 // READ: 2 x [P][PB][mstride] staged mask rows
-    const size_t mbuf = (size_t)p.P * C::PB * p.mstride;
+    uint8_t* M = reinterpret_cast<uint8_t*>(bars) + 64;                 // READ: 2 x [P][PB][mstride] staged mask rows;
+    const size_t mbuf = (size_t)p.P * C::PB * p.mstride;                // WRITE: NDBUF x [PB][MSP] sign bytes on their way to HBM
+    constexpr size_t wbuf = (size_t)C::PB * MSP;
     auto copy4 = [](uint8_t* dst, const uint8_t* src, bool ok) {
         asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(ok ? 4 : 0) : "memory");
     };
@@ -84,7 +93,7 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 
     if (tid == 0) {
         for (int i = 0; i < NSTAGE; i++) mbar_init(&bars[i], 1);
-        for (int i = 0; i < NDBUF; i++) mbar_init(&full[i], blockDim.x);
+        for (int i = 0; i < NDBUF; i++) mbar_init(&full[i], blockDim.x >> 5);     // one arrival per warp
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -96,8 +105,9 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     __shared__ float s_db[FLR_MAXT];
     const bool want_db = FLR_IS_READ(MODE) && p.db != nullptr;
     if (want_db) { for (int i = tid; i < FLR_MAXT; i += blockDim.x) s_db[i] = 0.f; }
-    auto store4 = [&](int plane, int o, int ox, const float* out) {
-        T* dst = yb + ((size_t)plane * p.OH + o) * p.OW + ox;
+    T* yplane = yb;                               // output plane of this thread (set per segment): h-down rows are written by the plane's own threads
+    auto store4 = [&](int /*plane*/, int o, int ox, const float* out) {
+        T* dst = yplane + (uint32_t)(o * p.OW + ox);
         if (vec_ok) store_quad<T>(dst, out);
         else {
 #pragma unroll
@@ -106,6 +116,9 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     };
 
     // this CTA's range of the global row space, processed segment by segment
+#ifdef FLR_TIMING
+    long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0}; long long tlast = clock64(); const long long tstart = tlast;
+#endif
     const int r0 = cta_cut(p, blockIdx.x, C::ALIGN, C::SNAP), r1 = cta_cut(p, blockIdx.x + 1, C::ALIGN, C::SNAP);
     int gs0 = 0;                                  // x stages issued by earlier segments (slot / parity bookkeeping)
     int db = 0; uint32_t dpar = 0;                // D buffer / full-barrier slot and phase parity of the NEXT body
@@ -123,42 +136,74 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 
         Stream<T, C, MODE, AFF> st;
         st.init(p, cg, tid, [&](int ch) { return Cvt<T>::get(reinterpret_cast<const T*>(p.b)[ch]); });
+        yplane = yb + (size_t)(cg.plane0 + st.unit) * p.OH * p.OW;
+        // per-thread bases of the segment: a body only adds its slot / buffer offsets
+        const T* const xbase = reinterpret_cast<const T*>(xst) + (size_t)st.unit * C::RS * p.bwx;
+        float* const Dbase = D + (size_t)st.unit * C::KO * p.dp;
+        const uint8_t* const Mrbase = M + (size_t)st.unit * C::PB * p.mstride;
+        const uint32_t stage_el = (uint32_t)p.stage_bytes / (uint32_t)sizeof(T), pq_el = (uint32_t)(C::PQ * p.bwx);
 
-        if (FLR_IS_READ(MODE)) stage_mask<C>(p, cg, cg.j_b0, tid, blockDim.x, M, copy4);
+        if (FLR_IS_READ(MODE) && st.active) stage_mask<C>(p, st.sm_lane, st.sm_dst, st.sm_src, cg.j_b0, M, copy4);
         mbar_wait(&bars[gs0 % NSTAGE], (uint32_t)((gs0 / NSTAGE) & 1));
         if (st.active) st.prologue(p, reinterpret_cast<const T*>(xst + (size_t)(gs0 % NSTAGE) * p.stage_bytes) + (size_t)st.unit * C::RS * p.bwx, cg.row0);
         if (FLR_IS_READ(MODE)) { asm volatile("cp.async.wait_all;" ::: "memory"); __syncthreads(); }
 
+        FLR_T(0)                                  // 0: segment set-up (TMA issue, init, first stage wait, prologue)
+        auto epilogue = [&](int kb, int buf) {     // h-down + sign-mask copy-out of finished body kb (D / staging buffer `buf`)
+#ifndef FLR_X_NOHDOWN
+            if (st.active) hdown_phase<T, C>(p, cg, cg.plane0 + st.unit, st.unit, st.g, kb, Dbase + buf * (uint32_t)dbuf, store4);
+#endif
+#ifndef FLR_X_NOMASKOUT
+            if (MODE == SIGN_WRITE && st.active) mask_out<C>(p, st.mo_src, st.mo_dst, cg.j_b0 + kb * C::PB, M + buf * (uint32_t)wbuf);
+#endif
+        };
         int pb = 0; uint32_t ppar = 0;            // slot / parity of the previous body
         for (int k = 0; k < cg.nbodies; k++) {
             const int s = 1 + k / C::M, slot = (gs0 + s) % NSTAGE, sub = k % C::M;
             if (k > 0) {
+#ifndef FLR_X_NOWAIT
                 mbar_wait(&full[pb], ppar);       // every thread has finished body k-1 (and the h-down of body k-3)
+#endif
+                FLR_T(1)                          // 1: wait for the other warps (full barrier)
                 if (tid == 0) {
                     const int consumed = 1 + k / C::M;
                     while (next_load < cg.nstages_total && next_load < consumed + NSTAGE) issue(next_load++);
                 }
             }
-            if (FLR_IS_READ(MODE) && k + 1 < cg.nbodies)                 // next body's mask rows, in flight during this body
-                stage_mask<C>(p, cg, cg.j_b0 + (k + 1) * C::PB, tid, blockDim.x, M + (size_t)((k + 1) & 1) * mbuf, copy4);
+            if (FLR_IS_READ(MODE) && k + 1 < cg.nbodies && st.active)    // next body's mask rows, in flight during this body
+                stage_mask<C>(p, st.sm_lane, st.sm_dst, st.sm_src, cg.j_b0 + (k + 1) * C::PB, M + ((k + 1) & 1) * (uint32_t)mbuf, copy4);
             if (sub == 0) mbar_wait(&bars[slot], (uint32_t)(((gs0 + s) / NSTAGE) & 1));
+            FLR_T(2)                              // 2: TMA issue, mask staging, x stage wait
             if (want_db) {                        // rows of this body that are real output rows (cf. hdown_phase: o = o0 - (ND-1) + k*KO + r)
                 const int lo = (C::ND - 1) - k * C::KO, hi = (cg.o1 - cg.o0) + (C::ND - 1) - k * C::KO;
                 st.db_lo = lo > 0 ? lo : 0; st.db_hi = hi < C::KO ? hi : C::KO;
             }
-            if (st.active)
-                st.body(p, reinterpret_cast<const T*>(xst + (size_t)slot * p.stage_bytes) + ((size_t)st.unit * C::RS + sub * C::PQ) * p.bwx,
-                        cg.row0 + s * C::RS + sub * C::PQ, cg.j_b0 + k * C::PB,
-                        D + db * dbuf + (size_t)st.unit * C::KO * p.dp,
-                        M + (size_t)(k & 1) * mbuf + (size_t)st.unit * C::PB * p.mstride);
+#ifndef FLR_X_NOBODY
+            if (st.active) {
+                const T* xt = xbase + slot * stage_el + sub * pq_el;
+                const int grow0 = cg.row0 + s * C::RS + sub * C::PQ;
+                float* Dk = Dbase + db * (uint32_t)dbuf;
+                const uint8_t* Mk = Mrbase + (k & 1) * (uint32_t)mbuf;
+                uint8_t* Mw = M + db * (uint32_t)wbuf + tid;
+                // bodies whose input rows all lie inside the plane (all but the first / last of a plane) skip the row-validity selects
+                const int jb = cg.j_b0 + k * C::PB;
+                if (!(grow0 >= 0 && grow0 + C::PQ <= p.H)) st.template body<true, -1>(p, xt, grow0, jb, Dk, Mk, Mw);
+                else if (C::UP == 2 && sizeof(T) == 4 && (p.xshift & 1)) st.template body<false, 1>(p, xt, grow0, jb, Dk, Mk, Mw);
+                else st.template body<false, 0>(p, xt, grow0, jb, Dk, Mk, Mw);
+            }
+#endif
             if (FLR_IS_READ(MODE)) asm volatile("cp.async.wait_all;" ::: "memory");
-            mbar_arrive(&full[db]);
-            if (k > 0) hdown_phase<T, C>(p, cg, tid, blockDim.x, k - 1, D + pb * dbuf, store4);
+            __syncwarp();
+            FLR_T(3)                              // 3: body
+            if ((tid & 31) == 0) mbar_arrive(&full[db]);
+            if (k > 0) epilogue(k - 1, pb);
+            FLR_T(4)                              // 4: h-down + mask copy-out
             pb = db; ppar = dpar;
             if (++db == NDBUF) { db = 0; dpar ^= 1u; }
         }
         mbar_wait(&full[pb], ppar);               // drain: h-down of the segment's last body
-        hdown_phase<T, C>(p, cg, tid, blockDim.x, cg.nbodies - 1, D + pb * dbuf, store4);
+        FLR_T(1)
+        epilogue(cg.nbodies - 1, pb);
         if (want_db) {
             // segmented warp reduction: lanes of one plane slot are contiguous
             const int lane = tid & 31;
@@ -178,9 +223,17 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 s_db[tid] = 0.f;
             }
         }
+        FLR_T(5)                                  // 5: drain h-down, db reduction
         gs0 += cg.nstages_total;
         gr += cg.o1 - cg.o0;
     }
+#ifdef FLR_TIMING
+    if ((tid & 31) == 0) {
+        long long* o = g_flr_prof + ((size_t)blockIdx.x * 16 + (tid >> 5)) * 8;
+        for (int i = 0; i < 6; i++) o[i] = tacc[i];
+        o[6] = clock64() - tstart; o[7] = tstart;
+    }
+#endif
 }
 
 // ---- driver entry point for tensor-map encoding (no -lcuda link dependency) ----------------------

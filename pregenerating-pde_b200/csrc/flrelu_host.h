@@ -101,9 +101,11 @@ static inline int make_plan(Plan& plan, int elem_size, int n, int c, int in_h, i
     }
     p.ncq_shift = -1;
     for (int s = 0; s < 16; s++) if ((1 << s) == p.ncq) p.ncq_shift = s;
+    p.hstep = p.G / p.ncq; if (p.hstep > 6) p.hstep = 6; if (p.hstep < 1) return -1;
     const int rs = variant_rs(up, down, ry);
     const int mstride = ((p.G + 4 + 3) / 4) * 4;                      // staged mask row (READ mode): G + 1 bytes at any 4-byte phase
     p.mstride = mstride; p.mnw = mstride / 4; p.mws = 0;
+    p.mlanes = p.G / p.mnw; if (p.mlanes < 1) p.mlanes = 1;
     // planes per CTA: fill up to FLR_MAXT threads (one big CTA per SM balances the four schedulers best), stay inside FLR_SMEM_KB
     int P = FLR_MAXT / p.G; if (P < 1) P = 1; if (P > p.NC) P = p.NC;
     {   // widest CTA (best scheduler balance, fewest wasted lanes) that still cuts the global row space into at least two
@@ -117,7 +119,9 @@ static inline int make_plan(Plan& plan, int elem_size, int n, int c, int in_h, i
     }
     for (;; P--) {
         const size_t stage = ((size_t)p.nbox * P * rs * bwx * elem_size + 127) / 128 * 128;
-        const size_t total = NSTAGE * stage + (size_t)NDBUF * P * 6 * p.dp * 4 + 64 + (size_t)2 * P * (6 * down) * mstride + 16;   // +16: read_code loads one word past a row
+        const size_t mread = (size_t)2 * P * (6 * down) * mstride + 16;      // READ staging, +16: read_code loads one word past a row
+        const size_t mwrite = (size_t)NDBUF * (6 * down) * MSP;               // WRITE staging (flrelu_core.h mask_out)
+        const size_t total = NSTAGE * stage + (size_t)NDBUF * P * 6 * p.dp * 4 + 64 + (mread > mwrite ? mread : mwrite);
         if (total <= FLR_SMEM_KB * 1024 || P == 1) { p.stage_bytes = (int)stage; plan.smem_bytes = total; break; }
     }
     if (plan.smem_bytes > 227 * 1024) return -1;

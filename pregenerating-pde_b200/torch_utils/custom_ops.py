@@ -9,6 +9,7 @@ library, so the reference's own op wrappers run on top of it unchanged (INTEGRAT
 import ctypes
 import weakref
 import numpy as np
+import os
 import torch
 
 from .. import _lib
@@ -59,6 +60,29 @@ def host_taps(f):
     taps = np.ascontiguousarray(f.detach().to('cpu', torch.float32).numpy())
     _host_taps[key] = (weakref.ref(f, lambda _r, k=key: _host_taps.pop(k, None)), f._version, taps)
     return taps
+
+
+# ---- profiler ranges (the reference wraps its ops in torch.autograd.profiler.record_function, torch_utils/misc.py:92-97)
+PROFILE_RANGES = bool(os.environ.get('CNO_NVTX'))      # off by default: a range costs host time on every call of the eager path
+
+
+def profiled(name):
+    """decorator: NVTX range + autograd-profiler record around an op entry point when CNO_NVTX=1 (or custom_ops.PROFILE_RANGES = True)"""
+    def wrap(fn):
+        def inner(*a, **k):
+            if not PROFILE_RANGES:
+                return fn(*a, **k)
+            with torch.autograd.profiler.record_function(name):
+                if torch.cuda.is_available():
+                    torch.cuda.nvtx.range_push(name)
+                try:
+                    return fn(*a, **k)
+                finally:
+                    if torch.cuda.is_available():
+                        torch.cuda.nvtx.range_pop()
+        inner.__name__, inner.__doc__, inner.__wrapped__ = fn.__name__, fn.__doc__, fn
+        return inner
+    return wrap
 
 
 class _BiasActPlugin:

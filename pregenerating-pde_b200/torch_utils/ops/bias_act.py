@@ -47,6 +47,7 @@ def _resolve(act, alpha, gain, clamp):
             float(-1 if clamp is None else clamp))
 
 
+@custom_ops.profiled('cno::bias_act')
 def bias_act(x, b=None, dim=1, act='linear', alpha=None, gain=None, clamp=None, impl='cuda'):
     """y = clamp(act(x + b) * gain).  Arguments as in the reference (bias_act.py:44-78)."""
     assert isinstance(x, torch.Tensor)

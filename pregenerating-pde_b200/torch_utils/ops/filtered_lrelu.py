@@ -46,6 +46,7 @@ def _check_scalars(up, down, gain, slope, clamp):
     assert clamp is None or (clamp == float(clamp) and clamp >= 0)
 
 
+@custom_ops.profiled('cno::filtered_lrelu')
 def filtered_lrelu(x, fu=None, fd=None, b=None, up=1, down=1, padding=0, gain=np.sqrt(2), slope=0.2, clamp=None,
                    flip_filter=False, impl='cuda'):
     """Arguments and semantics as in the reference (filtered_lrelu.py:48-108):

@@ -65,6 +65,7 @@ def setup_filter(f, device=torch.device('cpu'), normalize=True, flip_filter=Fals
     return (f * (gain ** (f.ndim / 2))).to(device=device)
 
 
+@custom_ops.profiled('cno::upfirdn2d')
 def upfirdn2d(x, f, up=1, down=1, padding=0, flip_filter=False, gain=1, impl='cuda'):
     """Arguments as in the reference (upfirdn2d.py:110-154)."""
     assert isinstance(x, torch.Tensor)

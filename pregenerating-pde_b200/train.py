@@ -34,6 +34,36 @@ def synthetic_fpo_batch(batch, size=128, device='cuda', seed=0, in_dim=7, out_di
     return t.to(device), x.contiguous().to(device, dtype), tgt.contiguous().to(device, dtype)
 
 
+class DeviceNSFlowBatcher:
+    """Device-resident sample construction of NSFlowTimeDataset (DataLoaders/CNO_TimeLoaders.py:183-248): the whole
+    trajectory array [N, T, H, W, 6] lives in HBM (the FPO set is a few GB; a B200 has 180 GB) and a batch of dataset indices
+    becomes (time, input, label) with three gathers and two fused elementwise ops on the GPU instead of a per-sample
+    `__getitem__` on the host plus a collate and an H2D copy.  Index arithmetic, z-scoring of (ux, uy, p) only, the lead-time
+    plane appended last and time = (t2 - t1) / 19 are the reference's."""
+
+    def __init__(self, data, time_indices, start=0, mean=None, std=None, time_input=True, device='cuda'):
+        self.data = torch.as_tensor(data, dtype=torch.float32).to(device)          # [N, T, H, W, 6]
+        self.pairs = torch.as_tensor(time_indices, dtype=torch.long, device=device)   # [multiplier, 2] = (t1, t2)
+        self.multiplier, self.start, self.time_input = len(time_indices), int(start), bool(time_input)
+        if mean is None or std is None:                                             # per-file statistics (:205-208)
+            mean = self.data[..., :3].mean(dim=(0, 1, 2, 3)); std = self.data[..., :3].std(dim=(0, 1, 2, 3), unbiased=False)
+        self.mean = torch.as_tensor(mean, dtype=torch.float32, device=device).view(1, 3, 1, 1)
+        self.std = torch.as_tensor(std, dtype=torch.float32, device=device).view(1, 3, 1, 1)
+
+    def batch(self, idx):
+        idx = torch.as_tensor(idx, dtype=torch.long, device=self.data.device)
+        i, k = idx // self.multiplier + self.start, idx % self.multiplier
+        t1, t2 = self.pairs[k, 0], self.pairs[k, 1]
+        time = (t2 - t1).float() / 19.0
+        inp = self.data[i, t1].permute(0, 3, 1, 2)                                  # [B, 6, H, W]
+        lab = self.data[i, t2][..., :3].permute(0, 3, 1, 2)
+        inp = torch.cat([(inp[:, :3] - self.mean) / self.std, inp[:, 3:]], 1)
+        lab = (lab - self.mean) / self.std
+        if self.time_input:
+            inp = torch.cat([inp, time.view(-1, 1, 1, 1).expand(-1, 1, inp.shape[2], inp.shape[3])], 1)
+        return time, inp.contiguous(), lab.contiguous()
+
+
 def freeze_dead_parameters(model):
     """decoder_inv[N_layers] is constructed but never called (CNO_timeModule_CIN.py:728-744 vs :867-878), which is why
     the reference needs strategy='ddp_find_unused_parameters_true'.  Parameters without a gradient are skipped by
@@ -48,13 +78,16 @@ def freeze_dead_parameters(model):
 class Trainer:
     """One optimisation step = forward, relative L1 (CNO_timeModule_CIN.py:939), backward, (all-reduce), AdamW (:996).
 
-    Data parallelism: batch sharding, the gradient all-reduce is the only exchange.  Every gradient lives in ONE
-    flat fp32 buffer (`p.grad` are views of it, laid out in reverse registration order = the order backward produces them), cut
-    into `buckets` contiguous ranges.  A post-accumulate hook counts the parameters of a bucket; when the last one has its
-    gradient the bucket's `ncclAllReduce(AVG)` is issued on a side stream, so it overlaps the rest of backward -- no
-    concatenation, no copy back, no scaling pass.  All of it is capturable: with `graph=True` the whole step (forward, backward,
-    bucketed all-reduces on the forked stream, AdamW) replays as one CUDA graph per rank.
-    `mode='finetune'`: CNO_FineTune.py workload (finetune.initialize_FT wrappers, three AdamW groups)."""
+    Data parallelism: batch sharding, the gradient all-reduce is the only exchange.  With more than one rank the
+    gradients travel through ONE flat fp32 buffer cut into `buckets` contiguous ranges (reverse registration order = the order
+    backward produces them).  A post-accumulate hook counts the parameters of a bucket; when the last one has its gradient the
+    bucket is gathered into the flat buffer with one multi-tensor copy, `p.grad` of its parameters become views of that range
+    (AdamW then reads the reduced values in place: no copy back, no scaling pass) and the bucket's `ncclAllReduce(AVG)` is issued
+    on a side stream, so it overlaps the rest of backward.  Gradients start every step as None: autograd hands over its own
+    buffers instead of adding into stale ones (an `add_` per parameter - 1,268 launches, 2.4 ms of the 31 ms step - when
+    `p.grad` pre-exists, profiles/r2_train_step_breakdown.txt).  A single rank does none of this.  All of it is capturable: with
+    `graph=True` the whole step (forward, backward, bucket copies + all-reduces on the forked stream, AdamW) replays as one
+    CUDA graph per rank.  `mode='finetune'`: CNO_FineTune.py workload (finetune.initialize_FT wrappers, three AdamW groups)."""
 
     def __init__(self, cfg=None, device='cuda', ddp=False, graph=False, autocast=None, buckets=4, mode='train', ft=None):
         self.device = torch.device(device)
@@ -72,26 +105,27 @@ class Trainer:
             with torch.no_grad():                      # same start on every rank
                 for p in self.model.parameters():
                     dist.broadcast(p, 0)
-        # ---- flat gradient buffer, bucketed -------------------------------------------------------------------------
-        order = self.params[::-1]
-        total = sum(p.numel() for p in order)
-        self.flat_grad = torch.zeros(total, dtype=torch.float32, device=self.device)
-        self.buckets = []                              # (start, end, parameter count)
-        nb = max(1, min(int(buckets), len(order)))
-        target, o, start, count = total / nb, 0, 0, 0
-        self._bucket_of = {}
-        for p in order:
-            p.grad = self.flat_grad[o:o + p.numel()].view_as(p)
-            self._bucket_of[p] = len(self.buckets)
-            o += p.numel(); count += 1
-            if o - start >= target and len(self.buckets) < nb - 1:
-                self.buckets.append((start, o, count)); start, count = o, 0
-        self.buckets.append((start, o, count))
-        self._pending = [c for _, _, c in self.buckets]
-        self._launched = [False] * len(self.buckets)
-        self.comm_stream = torch.cuda.Stream(self.device) if (self.world > 1 and self.device.type == 'cuda') else None
-        self.dp_mode = None
+        # ---- flat gradient buffer, bucketed (multi-rank only) -------------------------------------------------------
+        self.flat_grad, self.buckets, self._bucket_of, self._views = None, [], {}, {}
+        self.comm_stream, self.dp_mode = None, None
         if self.world > 1:
+            order = self.params[::-1]
+            total = sum(p.numel() for p in order)
+            self.flat_grad = torch.zeros(total, dtype=torch.float32, device=self.device)
+            nb = max(1, min(int(buckets), len(order)))
+            target, o, start, members = total / nb, 0, 0, []
+            for p in order:
+                self._views[p] = self.flat_grad[o:o + p.numel()].view_as(p)
+                self._bucket_of[p] = len(self.buckets)
+                members.append(p)
+                o += p.numel()
+                if o - start >= target and len(self.buckets) < nb - 1:
+                    self.buckets.append((start, o, members)); start, members = o, []
+            self.buckets.append((start, o, members))
+            self._pending = [len(m) for _, _, m in self.buckets]
+            self._launched = [False] * len(self.buckets)
+            if self.device.type == 'cuda':
+                self.comm_stream = torch.cuda.Stream(self.device)
             self.dp_mode = f'flat buffer, {len(self.buckets)} buckets, all-reduce(AVG) overlapped with backward'
             for p in order:
                 p.register_post_accumulate_grad_hook(self._grad_ready)
@@ -110,14 +144,21 @@ class Trainer:
 
     # ---- gradient exchange -------------------------------------------------------------------------------------------
     def _launch_bucket(self, b):
-        start, end, _ = self.buckets[b]
+        start, end, members = self.buckets[b]
         self._launched[b] = True
+        have = [p for p in members if p.grad is not None]
+        if len(have) < len(members):                   # a parameter without a gradient this step contributes zeros
+            self.flat_grad[start:end].zero_()
+        if have:
+            torch._foreach_copy_([self._views[p] for p in have], [p.grad for p in have])
+        for p in members:
+            p.grad = self._views[p]
         if self.comm_stream is None:                   # CPU / gloo: same arithmetic, no overlap
             dist.all_reduce(self.flat_grad[start:end])
             self.flat_grad[start:end].mul_(1.0 / self.world)
             return
         cur = torch.cuda.current_stream(self.device)
-        self.comm_stream.wait_stream(cur)              # the bucket's gradients are complete on the compute stream
+        self.comm_stream.wait_stream(cur)              # the bucket is complete on the compute stream
         with torch.cuda.stream(self.comm_stream):
             dist.all_reduce(self.flat_grad[start:end], op=dist.ReduceOp.AVG)
 
@@ -133,12 +174,19 @@ class Trainer:
                 self._launch_bucket(b)
         if self.comm_stream is not None:
             torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
-        self._pending = [c for _, _, c in self.buckets]
+        self._pending = [len(m) for _, _, m in self.buckets]
         self._launched = [False] * len(self.buckets)
+
+    def grad_vector(self):
+        """all gradients of the last step as one vector (reverse registration order); test / diagnostic helper"""
+        if self.flat_grad is not None:
+            return self.flat_grad.clone()
+        return torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1) for p in self.params[::-1]])
 
     # ---- step --------------------------------------------------------------------------------------------------------
     def _step_eager(self, t, x, y):
-        self.flat_grad.zero_()                          # one memset; p.grad stay views of the flat buffer
+        for p in self.params:
+            p.grad = None                               # autograd hands over its buffers: no add_ into stale gradients
         with torch.autocast(self.device.type, dtype=self.autocast, enabled=self.autocast is not None):
             pred = self.model(x, t)
         loss = self.model.training_loss(pred.float(), y.float())

@@ -28,6 +28,7 @@ static void run(const Plan& plan, const float* x, float* y, const float* bias) {
     };
     const size_t mbuf = (size_t)p.P * C::PB * p.mstride;
     std::vector<uint8_t> M(2 * mbuf + 16, 0xAA);                     // 0xAA = "clamped" everywhere: catches reads of unstaged bytes
+    std::vector<uint8_t> W((size_t)C::PB * MSP, 0xFF);                // WRITE: staged sign bytes of one body
     auto copy4 = [](uint8_t* dst, const uint8_t* src, bool ok) { if (ok) memcpy(dst, src, 4); else memset(dst, 0, 4); };
     auto store4 = [&](int plane, int o, int ox, const float* out) {
         for (int i = 0; i < 4; i++) if (ox + i < p.OW) y[((size_t)plane * p.OH + o) * p.OW + ox + i] = out[i];
@@ -41,24 +42,30 @@ static void run(const Plan& plan, const float* x, float* y, const float* bias) {
             int next_load = 0;
             auto issue = [&](int s) { tma((gs0 + s) % NSTAGE, cg.row0 + s * C::RS, cg.plane0); };
             while (next_load < cg.nstages_total && next_load < NSTAGE) issue(next_load++);
-            if (FLR_IS_READ(MODE)) for (int t = 0; t < nthreads; t++) stage_mask<C>(p, cg, cg.j_b0, t, nthreads, M.data(), copy4);
             for (int t = 0; t < nthreads; t++) {
                 th[t].init(p, cg, t, [&](int ch) { return bias[ch]; });
+                if (FLR_IS_READ(MODE) && th[t].active) stage_mask<C>(p, th[t].sm_lane, th[t].sm_dst, th[t].sm_src, cg.j_b0, M.data(), copy4);
                 if (th[t].active) th[t].prologue(p, xst.data() + (size_t)(gs0 % NSTAGE) * stage_el + (size_t)th[t].unit * C::RS * p.bwx, cg.row0);
             }
             for (int k = 0; k < cg.nbodies; k++) {
                 const int s = 1 + k / C::M, slot = (gs0 + s) % NSTAGE;
-                if (FLR_IS_READ(MODE) && k + 1 < cg.nbodies) for (int t = 0; t < nthreads; t++)
-                    stage_mask<C>(p, cg, cg.j_b0 + (k + 1) * C::PB, t, nthreads, M.data() + (size_t)((k + 1) & 1) * mbuf, copy4);
-                for (int t = 0; t < nthreads; t++) if (th[t].active)
-                    th[t].body(p, xst.data() + (size_t)slot * stage_el + ((size_t)th[t].unit * C::RS + (k % C::M) * C::PQ) * p.bwx,
-                               cg.row0 + s * C::RS + (k % C::M) * C::PQ, cg.j_b0 + k * C::PB,
-                               D.data() + ((size_t)(k & 1) * p.P + th[t].unit) * C::KO * p.dp,
-                               M.data() + (size_t)(k & 1) * mbuf + (size_t)th[t].unit * C::PB * p.mstride);
+                if (FLR_IS_READ(MODE) && k + 1 < cg.nbodies) for (int t = 0; t < nthreads; t++) if (th[t].active)
+                    stage_mask<C>(p, th[t].sm_lane, th[t].sm_dst, th[t].sm_src, cg.j_b0 + (k + 1) * C::PB, M.data() + (size_t)((k + 1) & 1) * mbuf, copy4);
+                const int grow0 = cg.row0 + s * C::RS + (k % C::M) * C::PQ;
+                const bool interior = grow0 >= 0 && grow0 + C::PQ <= p.H;
+                for (int t = 0; t < nthreads; t++) if (th[t].active) {
+                    const float* xt = xst.data() + (size_t)slot * stage_el + ((size_t)th[t].unit * C::RS + (k % C::M) * C::PQ) * p.bwx;
+                    float* Dk = D.data() + ((size_t)(k & 1) * p.P + th[t].unit) * C::KO * p.dp;
+                    const uint8_t* Mk = M.data() + (size_t)(k & 1) * mbuf + (size_t)th[t].unit * C::PB * p.mstride;
+                    if (interior) th[t].template body<false, 0>(p, xt, grow0, cg.j_b0 + k * C::PB, Dk, Mk, W.data() + t);
+                    else th[t].template body<true, -1>(p, xt, grow0, cg.j_b0 + k * C::PB, Dk, Mk, W.data() + t);
+                }
+                if (MODE == SIGN_WRITE) for (int t = 0; t < nthreads; t++) if (th[t].active) mask_out<C>(p, th[t].mo_src, th[t].mo_dst, cg.j_b0 + k * C::PB, W.data());
                 const int consumed = 1 + (k + 1) / C::M;
                 while (next_load < cg.nstages_total && next_load < consumed + NSTAGE) issue(next_load++);
-                for (int t = 0; t < nthreads; t++)
-                    hdown_phase<float, C>(p, cg, t, nthreads, k, D.data() + (size_t)(k & 1) * p.P * C::KO * p.dp, store4);
+                for (int t = 0; t < nthreads; t++) if (th[t].active)
+                    hdown_phase<float, C>(p, cg, cg.plane0 + th[t].unit, th[t].unit, th[t].g, k,
+                                          D.data() + ((size_t)(k & 1) * p.P + th[t].unit) * C::KO * p.dp, store4);
             }
             gs0 += cg.nstages_total;
             gr += cg.o1 - cg.o0;

@@ -17,7 +17,7 @@ dist.init_process_group('gloo', rank=rank, world_size=world)
 cfg = dict(in_dim=7, in_size=16, N_layers=1, N_res=1, N_res_neck=1, channel_multiplier=4, out_dim=3, is_time=1, nl_dim=[2, 3], latent_lift_proj_dim=8, lr=1e-2)
 torch.manual_seed(0)
 tr = train.Trainer(cfg, device='cpu', ddp=world > 1, buckets=3)
-assert len(tr.buckets) == 3 and all(p.grad.untyped_storage().data_ptr() == tr.flat_grad.untyped_storage().data_ptr() for p in tr.params)
+assert (len(tr.buckets) == 3 and tr.flat_grad is not None) if world > 1 else (tr.flat_grad is None and not tr.buckets)   # a single rank keeps no flat buffer
 g = torch.Generator().manual_seed(3)
 with torch.no_grad():
     for p in tr.model.parameters():
@@ -26,15 +26,17 @@ t, x, y = train.synthetic_fpo_batch(4, size=16, device='cpu', seed=5)
 y[2:] = y[:2].flip(0).abs() * y[2:].sign()            # both shards have the same mean |y| -> identical loss denominators
 n = 4 // world
 sl = slice(rank * n, (rank + 1) * n)
-tr.flat_grad.zero_()
+for p in tr.params:
+    p.grad = None
 loss = tr.model.training_loss(tr.model(x[sl], t[sl]), y[sl])
 loss.backward()                                        # the hooks launch each bucket's all-reduce as soon as it is complete
 if world > 1:
     assert any(tr._launched), 'no bucket was reduced from inside backward'
     tr._finish_allreduce()
 grads = {k: p.grad.detach().clone() for k, p in tr.model.named_parameters() if p.requires_grad}
-assert all(p.grad.untyped_storage().data_ptr() == tr.flat_grad.untyped_storage().data_ptr() for p in tr.params)   # still views
-l2 = tr.step(t[sl], x[sl], y[sl])                       # a whole step (zero, forward, backward, reduce, AdamW) runs on the reduced gradients
+if world > 1:                                          # after the reduce every gradient is a view of the flat buffer (AdamW reads it in place)
+    assert all(p.grad.untyped_storage().data_ptr() == tr.flat_grad.untyped_storage().data_ptr() for p in tr.params)
+l2 = tr.step(t[sl], x[sl], y[sl])                       # a whole step (grads to None, forward, backward, gather + reduce, AdamW)
 if rank == 0:
     torch.save(grads, os.environ['CNO_OUT'])
 dist.destroy_process_group()

@@ -117,6 +117,40 @@ def test_filtered_lrelu_sweep(cno, name, s_in, s_out, N, C, dtype):
     assert n_all <= max(2 if dtype == torch.float32 else 16, bad.numel() // 100000)
 
 
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize('name,s_in,s_out,N,C', [('I', 8, 8, 5, 37), ('I', 16, 16, 3, 9), ('D', 16, 8, 2, 11), ('U', 8, 16, 3, 7), ('I', 12, 12, 2, 5)])
+def test_filtered_lrelu_small_planes_both_kernels(cno, name, s_in, s_out, N, C, dtype):
+    """Up-res planes of at most 64 columns have two kernels behind the same entry point (include/cno_b200.h): the whole-plane
+    kernel (default) and the streaming kernel.  Both must match the oracle, and each other's sign masks byte for byte wherever
+    the pre-activation is not at rounding distance from zero (plane counts that do not divide the CTA's plane group included)."""
+    cfg = O.lrelu_config(s_in, s_out)
+    g = torch.Generator().manual_seed(11 * s_in + s_out + C)
+    x = torch.randn(N, C, s_in, s_in, generator=g).to(dtype).float()
+    b = torch.randn(C, generator=g).to(dtype).float()
+    dy = torch.randn(N, C, s_out, s_out, generator=g).to(dtype).float()
+    xr, br = x.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    y_ref = O.filtered_lrelu(xr, cfg['fu'], cfg['fd'], br, up=cfg['up'], down=cfg['down'], padding=cfg['padding'])
+    dx_ref, db_ref = torch.autograd.grad(y_ref, [xr, br], dy)
+    lib = cno._lib.load()
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
+    out = {}
+    prev = lib.cno_filtered_lrelu_plane_kernel(-1)
+    try:
+        for on in (1, 0):
+            lib.cno_filtered_lrelu_plane_kernel(on)
+            y, dx, db, mask = fl_case(cno, x, b, dy, cfg, dtype)
+            assert max(rel(y, y_ref), rel(dx, dx_ref), rel(db, db_ref)) < tol, (on, rel(y, y_ref), rel(dx, dx_ref), rel(db, db_ref))
+            out[on] = (y, dx, db, mask)
+    finally:
+        lib.cno_filtered_lrelu_plane_kernel(prev)
+    v = O.filtered_lrelu_preact(x, cfg['fu'], b, up=cfg['up'], padding=cfg['padding'])
+    sh, swb, swv = O.sign_mask_shape(y_ref.shape[2:], cfg['fd'], cfg['down'])
+    far = (v[:, :, :sh, :swv].abs() > 1e-5)
+    ca, cb = O.unpack_sign_mask(out[1][3].cpu(), swv), O.unpack_sign_mask(out[0][3].cpu(), swv)
+    assert int(((ca != cb) & far).sum()) == 0
+    assert torch.equal(out[1][3][..., swv // 4 + 1:], out[0][3][..., swv // 4 + 1:])       # row padding bytes: zero from both
+
+
 def test_filtered_lrelu_generic_golden(cno, golden):
     """clamp + flip + 8-tap filters: no fused variant -> generic composition on our kernels."""
     g = golden['filtered_lrelu']

@@ -6,7 +6,7 @@ cd "$(dirname "$0")/.."
 name=$1; flags=$2
 mkdir -p build/var_$name tools/variants
 cd pregenerating-pde_b200/csrc
-for f in capi bias_act upfirdn2d flrelu_act cin flrelu_fused flrelu_fused_f32; do
+for f in capi bias_act upfirdn2d flrelu_act cin flrelu_fused flrelu_fused_f32 flrelu_plane_f32; do
   nvcc -std=c++17 -O3 -gencode arch=compute_100a,code=sm_100a -lineinfo -Xcompiler -fPIC -DFLR_QUICK $flags -c $f.cu -o ../../build/var_$name/$f.o &
 done
 wait
