@@ -20,6 +20,10 @@ CFG = dict(in_dim=5, in_size=32, N_layers=2, N_res=1, N_res_neck=2, channel_mult
 GRAD_KEYS = ['lift.inter_CNOBlock.activation.bias', 'encoder.0.in_norm_conditiner.norm.weight',
              'res_nets.1.in_norm_conditiner2.lat2scale.weight', 'decoder.1.convolution.weight',
              'project.convolution.bias', 'ED_expansion.0.activation.bias']
+# convolution biases in front of an instance-norm CIN: mathematically zero gradient (the per-plane mean removes the bias); the
+# reference's values are stored to show that they are round-off noise (tests/test_cno_model.py, cin.conv_before_film)
+DEAD_BIAS_KEYS = ['encoder.0.convolution.bias', 'decoder.1.convolution.bias', 'res_nets.0.convolution1.bias',
+                  'res_nets.0.convolution2.bias', 'ED_expansion.1.convolution.bias']
 
 
 def main():
@@ -44,9 +48,16 @@ def main():
     out.update({'x': x.numpy(), 't': t.numpy(), 'target': target.numpy(), 'y': y.detach().numpy(), 'loss': np.float64(loss.item())})
     for k in GRAD_KEYS:
         out['grad.' + k] = named[k].grad.numpy()
+    for k in DEAD_BIAS_KEYS:
+        out['deadgrad.' + k] = named[k].grad.numpy()
+    out['grad_scale'] = np.float64(max(float(p.grad.abs().max()) for p in named.values() if p.grad is not None))
     out['no_grad_params'] = np.array(sorted(k for k, p in named.items() if p.grad is None))
     out['n_params'] = np.int64(sum(p.numel() for p in model.parameters()))
-    np.savez_compressed(os.path.join(mg.OUT, 'cno_model.npz'), **out)
+    path = os.path.join(mg.OUT, 'cno_model.npz')
+    if os.path.exists(path) and '--all' not in sys.argv:     # keep committed arrays (the CPU convolution backend differs by 1e-6 from run
+        old = dict(np.load(path))                             # to run with the thread count); only new keys are added
+        out = {**out, **old}
+    np.savez_compressed(path, **out)
     print('cno_model.npz:', len(sd), 'tensors,', int(out['n_params']), 'parameters, loss', float(loss))
 
 

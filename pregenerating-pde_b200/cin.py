@@ -218,6 +218,24 @@ def film_forward(self, x, timestep, residual=None):
     return y if residual is None else residual + y
 
 
+SKIP_DEAD_BIAS = os.environ.get('CNO_KEEP_CONV_BIAS', '0') == '0'
+
+
+def conv_before_film(conv, film, x):
+    """conv(x) for a convolution whose output goes straight into `film` (CNOBlock.forward, CNO_timeModule_CIN.py:329-333;
+    ResidualBlock.forward :496-505).  An instance norm subtracts the per-plane mean, so a per-channel constant added in front of
+    it vanishes exactly: InstanceNorm(conv(x) + b) == InstanceNorm(conv(x)), and d loss / d b == 0.  The reference still runs
+    the bias add (one elementwise launch) and, in backward, the reduction that produces a gradient of pure round-off noise;
+    at the TrainCNO_time_L configuration that is 97 x 2 launches and 2.8 ms of the 28 ms training step.  Here the convolution
+    runs without the bias and the parameter simply gets no gradient (AdamW skips it; its value stays what the checkpoint
+    says).  Only for the per-plane flavour of FILM (nl_dim = [2, 3], no running statistics); CNO_KEEP_CONV_BIAS=1 restores the add."""
+    norm = getattr(film, 'norm', None)
+    if (SKIP_DEAD_BIAS and conv.bias is not None and isinstance(norm, torch.nn.InstanceNorm2d) and not norm.track_running_stats
+            and isinstance(conv, torch.nn.Conv2d) and type(conv).forward is torch.nn.Conv2d.forward and conv.padding_mode == 'zeros'):
+        return torch.nn.functional.conv2d(x, conv.weight, None, conv.stride, conv.padding, conv.dilation, conv.groups)
+    return conv(x)
+
+
 def _film_kernel_ok(self, x, timestep):
     norm = self.norm
     return (x.is_cuda and x.ndim == 4 and isinstance(norm, torch.nn.InstanceNorm2d) and norm.affine

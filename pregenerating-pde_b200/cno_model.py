@@ -147,10 +147,10 @@ class CNOBlock(nn.Module):
             self.in_norm_conditiner = FILM(out_channels, dim=nl_dim, s=in_size)
 
     def forward(self, x, time):
-        x = self.convolution(x)
         if self.is_time:
+            x = _cin.conv_before_film(self.convolution, self.in_norm_conditiner, x)       # the bias would vanish in the instance norm
             return _cin.film_lrelu(self.in_norm_conditiner, self.activation, x, time)     # CIN folded into the activation's prologue
-        return self.activation(x)
+        return self.activation(self.convolution(x))
 
 
 class LiftProjectBlock(nn.Module):
@@ -184,14 +184,12 @@ class ResidualBlock(nn.Module):
             self.in_norm_conditiner2 = FILM(channels, dim=nl_dim, s=size)
 
     def forward(self, x, time):
-        out = self.convolution1(x)
         if self.is_time:
-            out = self.convolution2(_cin.film_lrelu(self.in_norm_conditiner1, self.activation, out, time))
-        else:
-            out = self.convolution2(self.activation(out))
-        if self.is_time:
+            out = _cin.conv_before_film(self.convolution1, self.in_norm_conditiner1, x)
+            out = _cin.film_lrelu(self.in_norm_conditiner1, self.activation, out, time)
+            out = _cin.conv_before_film(self.convolution2, self.in_norm_conditiner2, out)
             return self.in_norm_conditiner2(out, time, residual=x)      # x + CIN(out) in the CIN kernel's single pass
-        return x + out
+        return x + self.convolution2(self.activation(self.convolution1(x)))
 
 
 class CNO_time(nn.Module):

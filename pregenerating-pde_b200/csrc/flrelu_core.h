@@ -97,13 +97,16 @@ template <> struct Cvt<float> { static FLR_DEV float get(float v) { return v; } 
 #define FLR_MINB 1              // resident CTAs per SM the register budget is sized for
 #endif
 #ifndef FLR_SMEM_KB
-#define FLR_SMEM_KB 212         // shared memory budget per CTA
+#define FLR_SMEM_KB 222         // dynamic shared memory budget per CTA (227 KB per block on sm_100 minus the 2 KB static s_db and slack)
 #endif
 constexpr int NSTAGE = FLR_NSTAGE;
 constexpr int NDBUF = 3;           // D buffers (finished v-down rows) in flight, see flr_fused_kernel
-constexpr int MSP = FLR_MAXT;      // WRITE: row pitch of the staged sign bytes, layout [up-res row of the body][thread]: a thread's
+constexpr int MSP = FLR_MAXT;      // WRITE (DOWN = 2): row pitch of the staged sign bytes, layout [up-res row of the body][thread]: a thread's
                                    // byte of row jl sits at the compile-time offset jl * MSP from its own slot (one STS.U8, no
-                                   // address arithmetic); mask_out() copies finished bodies to HBM with 32-bit stores
+                                   // address arithmetic); mask_out() copies finished bodies to HBM with 32-bit stores.  DOWN = 4 bodies
+                                   // have 24 rows: three such buffers would cost 36 KB and halve the planes per CTA of the wide D
+                                   // configuration, so they use the runtime pitch Params::msp (one pointer step per row instead)
+template <class C> FLR_DEV int stage_pitch(int msp) { return C::DOWN == 4 ? msp : MSP; }
 
 // Everything the kernel needs besides the tensor map.  Filled by the host (flrelu_fused.cu).
 struct Params {
@@ -129,6 +132,7 @@ struct Params {
                                // writers (consecutive f) and the h-down readers (f = DOWN*cq + i) are both bank-conflict free and
                                // a reader's NF4 loads are constant offsets from one address
     int ncq, ncq_shift;        // output column quads per row = ceil(OW/4); log2 when a power of two, else -1
+    int msp;                   // WRITE, DOWN = 4: row pitch of the staged sign bytes = threads rounded up to 16 (stage_pitch)
     int hstep;                 // h-down: row lanes per plane slot = min(G / ncq, KO) (hdown_phase)
     int stage_bytes;           // bytes of one x stage (multiple of 128)
     int mask_h, mask_w, mask_pitch, sx, sy;
@@ -265,7 +269,7 @@ struct Stream {
             FLR_UNROLL for (int m = 0; m < 4; m++) if (4 * g + m < p.UW) colmask |= 1u << (2 * m);   // bit 0 of each 2-bit code
             {   // mask_out role: G/4 word columns x 4 row lanes per plane slot
                 const int nwr = p.G >> 2, jl0 = g / nwr, wc = g - jl0 * nwr;
-                mo_src = jl0 * MSP + unit * p.G + 4 * wc;
+                mo_src = jl0 * stage_pitch<C>(p.msp) + unit * p.G + 4 * wc;
                 mo_dst = p.mask + ((int64_t)plane * p.mask_h + jl0) * p.mask_pitch + 4 * wc;
             }
         } else if (FLR_IS_READ(MODE)) {
@@ -389,7 +393,7 @@ struct Stream {
                 v[1] = ffma2(win[(phi > C::RY ? 1 : 0) + k][1], t, v[1]);
             }
             act(p, v, code);
-            if (MODE == SIGN_WRITE) Mst[jl * MSP] = (uint8_t)code;      // staged; rows beyond UH are dropped by mask_out()
+            if (MODE == SIGN_WRITE) Mst[jl * stage_pitch<C>(p.msp)] = (uint8_t)code;      // staged; rows beyond UH are dropped by mask_out()
             (void)j;
             // vertical down-FIR, scatter form: row r of this body completes at jl = DOWN*r + DOWN-1
             FLR_UNROLL for (int r = 0; r < C::ND; r++) {
@@ -444,11 +448,12 @@ FLR_DEV void stage_mask(const Params& p, int sm_lane, int sm_dst, const uint8_t*
 // ------------------------------------------------------------------------------------------------
 template <class C>
 FLR_DEV void mask_out(const Params& p, int mo_src, uint8_t* mo_dst, int jb, const uint8_t* Mbuf) {
-    const int jl0 = mo_src / MSP;                           // MSP is a power of two
+    const int sp = stage_pitch<C>(p.msp);
+    const int jl0 = mo_src / sp;                            // 0..3 (MSP is a power of two; DOWN = 4 divides once per body)
     int rows = p.UH - jb; if (rows > C::PB) rows = C::PB;
     const uint8_t* src = Mbuf + mo_src;
     uint32_t w[C::PB / 4];
-    FLR_UNROLL for (int it = 0; it < C::PB / 4; it++) w[it] = *reinterpret_cast<const uint32_t*>(src + 4 * it * MSP);
+    FLR_UNROLL for (int it = 0; it < C::PB / 4; it++) w[it] = *reinterpret_cast<const uint32_t*>(src + 4 * it * sp);
     uint8_t* dst = mo_dst + (uint32_t)(jb * p.mask_pitch);
     FLR_UNROLL for (int it = 0; it < C::PB / 4; it++) {
         if (jl0 + 4 * it < rows) *reinterpret_cast<uint32_t*>(dst) = w[it];

@@ -83,7 +83,7 @@ flr_fused_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     uint64_t* full = bars + NSTAGE;
     uint8_t* M = reinterpret_cast<uint8_t*>(bars) + 64;                 // READ: 2 x [P][PB][mstride] staged mask rows;
     const size_t mbuf = (size_t)p.P * C::PB * p.mstride;                // WRITE: NDBUF x [PB][MSP] sign bytes on their way to HBM
-    constexpr size_t wbuf = (size_t)C::PB * MSP;
+    const size_t wbuf = (size_t)C::PB * stage_pitch<C>(p.msp);
     auto copy4 = [](uint8_t* dst, const uint8_t* src, bool ok) {
         asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(ok ? 4 : 0) : "memory");
     };

@@ -120,9 +120,10 @@ static inline int make_plan(Plan& plan, int elem_size, int n, int c, int in_h, i
     for (;; P--) {
         const size_t stage = ((size_t)p.nbox * P * rs * bwx * elem_size + 127) / 128 * 128;
         const size_t mread = (size_t)2 * P * (6 * down) * mstride + 16;      // READ staging, +16: read_code loads one word past a row
-        const size_t mwrite = (size_t)NDBUF * (6 * down) * MSP;               // WRITE staging (flrelu_core.h mask_out)
+        const int msp = down == 4 ? (P * p.G + 15) / 16 * 16 : MSP;            // WRITE staging pitch (flrelu_core.h stage_pitch)
+        const size_t mwrite = (size_t)NDBUF * (6 * down) * msp;
         const size_t total = NSTAGE * stage + (size_t)NDBUF * P * 6 * p.dp * 4 + 64 + (mread > mwrite ? mread : mwrite);
-        if (total <= FLR_SMEM_KB * 1024 || P == 1) { p.stage_bytes = (int)stage; plan.smem_bytes = total; break; }
+        if (total <= FLR_SMEM_KB * 1024 || P == 1) { p.stage_bytes = (int)stage; p.msp = msp; plan.smem_bytes = total; break; }
     }
     if (plan.smem_bytes > 227 * 1024) return -1;
     p.P = P;

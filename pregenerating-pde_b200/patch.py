@@ -54,7 +54,7 @@ def _cno_block_forward(self, x, time):
     timed = self.is_time == 1 or self.is_time is True
     if not (timed and isinstance(self.batch_norm, torch.nn.Identity)):
         return _saved['cno_block_forward'](self, x, time)
-    return _cin.film_lrelu(self.in_norm_conditiner, self.activation, self.convolution(x), time)
+    return _cin.film_lrelu(self.in_norm_conditiner, self.activation, _cin.conv_before_film(self.convolution, self.in_norm_conditiner, x), time)
 
 
 def _residual_forward(self, x, time):
@@ -64,7 +64,8 @@ def _residual_forward(self, x, time):
     timed = self.is_time == 1 or self.is_time is True
     if not (timed and isinstance(self.batch_norm1, torch.nn.Identity) and isinstance(self.batch_norm2, torch.nn.Identity)):
         return _saved['residual_forward'](self, x, time)
-    out = self.convolution2(_cin.film_lrelu(self.in_norm_conditiner1, self.activation, self.convolution1(x), time))
+    out = _cin.film_lrelu(self.in_norm_conditiner1, self.activation, _cin.conv_before_film(self.convolution1, self.in_norm_conditiner1, x), time)
+    out = _cin.conv_before_film(self.convolution2, self.in_norm_conditiner2, out)
     return self.in_norm_conditiner2(out, time, residual=x)
 
 

@@ -65,13 +65,26 @@ class DeviceNSFlowBatcher:
 
 
 def freeze_dead_parameters(model):
-    """decoder_inv[N_layers] is constructed but never called (CNO_timeModule_CIN.py:728-744 vs :867-878), which is why
-    the reference needs strategy='ddp_find_unused_parameters_true'.  Parameters without a gradient are skipped by
-    AdamW either way, so marking them frozen changes nothing numerically and lets DDP run without the search."""
-    dead = model.decoder_inv[model.N_layers]
+    """Parameters that never receive a gradient are marked frozen: AdamW skips a parameter without gradient either way, so this
+    changes nothing numerically, but DDP needs no unused-parameter search and the gradient buckets complete during backward.
+    (1) decoder_inv[N_layers] is constructed but never called (CNO_timeModule_CIN.py:728-744 vs :867-878), which is why the
+    reference needs strategy='ddp_find_unused_parameters_true'.  (2) Convolution biases in front of an instance-norm CIN
+    (cin.conv_before_film): the convolution runs without them, their reference gradient is round-off noise."""
+    from . import cin as _cin
     n = 0
-    for p in dead.parameters():
+    for p in model.decoder_inv[model.N_layers].parameters():
         p.requires_grad_(False); n += p.numel()
+    if _cin.SKIP_DEAD_BIAS:
+        inst = lambda f: isinstance(getattr(f, 'norm', None), nn.InstanceNorm2d) and not f.norm.track_running_stats
+        for m in model.modules():
+            pairs = []
+            if isinstance(m, cno_model.CNOBlock) and m.is_time:
+                pairs = [(m.convolution, m.in_norm_conditiner)]
+            elif isinstance(m, cno_model.ResidualBlock) and m.is_time:
+                pairs = [(m.convolution1, m.in_norm_conditiner1), (m.convolution2, m.in_norm_conditiner2)]
+            for conv, film in pairs:
+                if conv.bias is not None and inst(film) and conv.bias.requires_grad:
+                    conv.bias.requires_grad_(False); n += conv.bias.numel()
     return n
 
 

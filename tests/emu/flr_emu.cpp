@@ -28,7 +28,7 @@ static void run(const Plan& plan, const float* x, float* y, const float* bias) {
     };
     const size_t mbuf = (size_t)p.P * C::PB * p.mstride;
     std::vector<uint8_t> M(2 * mbuf + 16, 0xAA);                     // 0xAA = "clamped" everywhere: catches reads of unstaged bytes
-    std::vector<uint8_t> W((size_t)C::PB * MSP, 0xFF);                // WRITE: staged sign bytes of one body
+    std::vector<uint8_t> W((size_t)C::PB * stage_pitch<C>(p.msp), 0xFF);                // WRITE: staged sign bytes of one body
     auto copy4 = [](uint8_t* dst, const uint8_t* src, bool ok) { if (ok) memcpy(dst, src, 4); else memset(dst, 0, 4); };
     auto store4 = [&](int plane, int o, int ox, const float* out) {
         for (int i = 0; i < 4; i++) if (ox + i < p.OW) y[((size_t)plane * p.OH + o) * p.OW + ox + i] = out[i];

@@ -87,12 +87,74 @@ def _check(golden, dev, tol, backend_dev=None):
     assert sorted(k for k, p in named.items() if p.grad is None) == list(g['no_grad_params'])
 
 
-def test_mirror_matches_reference_cpu(golden):
+@pytest.fixture
+def keep_conv_bias():
+    """the golden comparison runs the convolutions WITH their bias, like the reference (bit-identical convolution path on the CPU);
+    the bias-free form has its own test below"""
+    from pregenerating_pde_b200 import cin
+    prev, cin.SKIP_DEAD_BIAS = cin.SKIP_DEAD_BIAS, False
+    yield
+    cin.SKIP_DEAD_BIAS = prev
+
+
+def test_mirror_matches_reference_cpu(golden, keep_conv_bias):
     _check(golden, 'cpu', 2e-5)
 
 
+def _dead_bias_check(golden, dev, tol):
+    """cin.conv_before_film: a convolution bias in front of an instance-norm CIN vanishes in the per-plane mean, so the package
+    runs the convolution without it.  Claims checked: (1) the reference's OWN gradient of such a bias (golden file) is round-off
+    noise, (2) output and all other gradients are unchanged.  (2) uses a smooth loss: the model's relative-L1 loss has the
+    gradient sign(pred - target), where a 1e-7 change of pred flips signs and moves cancellation-heavy sums by 1e-3."""
+    from pregenerating_pde_b200 import cin
+    g, sd = _load(golden)
+    gscale = float(g['grad_scale'])
+    x, t, target = (torch.from_numpy(g[k]).to(dev) for k in ('x', 't', 'target'))
+    res = {}
+    prev = cin.SKIP_DEAD_BIAS
+    try:
+        for skip in (False, True):
+            cin.SKIP_DEAD_BIAS = skip
+            model = _build(dev)
+            model.load_state_dict(sd, strict=True)
+            y = model(x, t)
+            ((y - target) ** 2).mean().backward()
+            res[skip] = (y.detach(), {k: p.grad for k, p in model.named_parameters()})
+    finally:
+        cin.SKIP_DEAD_BIAS = prev
+    assert _rel(res[True][0], res[False][0].cpu().numpy()) < tol
+    gs = max(float(v.abs().max()) for v in res[False][1].values() if v is not None)
+    dead = [k for k, v in res[True][1].items() if v is None and res[False][1][k] is not None]
+    assert len(dead) >= 10 and all(k.endswith(('convolution.bias', 'convolution1.bias', 'convolution2.bias')) for k in dead)
+    stored = [k[9:] for k in g.files if k.startswith('deadgrad.')]
+    assert len(stored) >= 5 and set(stored) <= set(dead)
+    for k in stored:                                           # the unmodified reference's own gradients of these biases
+        assert float(abs(g['deadgrad.' + k]).max()) < 1e-5 * gscale, (k, 'reference gradient is not noise')
+    for k in dead:
+        assert float(res[False][1][k].abs().max()) < 1e-5 * gs
+    # all other gradients: equal up to the leaky-ReLU kinks (a pre-activation within 1e-7 of zero changes slope 1 <-> 0.2 when the
+    # rounding of the convolution changes; each such flip is a finite jump of the gradient), hence an L2 and a loose max bound
+    num = sum(float(((v - res[False][1][k]) ** 2).sum()) for k, v in res[True][1].items() if v is not None)
+    den = sum(float((res[False][1][k] ** 2).sum()) for k, v in res[True][1].items() if v is not None)
+    assert (num / den) ** 0.5 < 2e-3, (num / den) ** 0.5
+    for k, v in res[True][1].items():
+        if v is not None:
+            assert float((v - res[False][1][k]).abs().max()) < 1e-2 * gs, k
+
+
+def test_dead_conv_bias_is_exact_algebra_cpu(golden):
+    _dead_bias_check(golden, 'cpu', 2e-5)
+
+
 @pytest.mark.gpu
-def test_mirror_matches_reference_gpu(golden):
+def test_dead_conv_bias_is_exact_algebra_gpu(golden):
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    _dead_bias_check(golden, 'cuda', 5e-5)
+
+
+@pytest.mark.gpu
+def test_mirror_matches_reference_gpu(golden, keep_conv_bias):
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
     _check(golden, 'cuda', 5e-5, backend_dev=_torch_backend_deviation(golden, 'cuda'))

@@ -33,7 +33,7 @@ loss.backward()                                        # the hooks launch each b
 if world > 1:
     assert any(tr._launched), 'no bucket was reduced from inside backward'
     tr._finish_allreduce()
-grads = {k: p.grad.detach().clone() for k, p in tr.model.named_parameters() if p.requires_grad}
+grads = {k: (p.grad.detach().clone() if p.grad is not None else torch.zeros_like(p)) for k, p in tr.model.named_parameters() if p.requires_grad}   # no gradient: a convolution bias in front of a CIN (cin.conv_before_film)
 if world > 1:                                          # after the reduce every gradient is a view of the flat buffer (AdamW reads it in place)
     assert all(p.grad.untyped_storage().data_ptr() == tr.flat_grad.untyped_storage().data_ptr() for p in tr.params)
 l2 = tr.step(t[sl], x[sl], y[sl])                       # a whole step (grads to None, forward, backward, gather + reduce, AdamW)

@@ -39,8 +39,9 @@ import pregenerating_pde_b200 as cno
 def run(block, x, t):
     xr = x.clone().requires_grad_(True)
     y = block(xr, t)
-    g = torch.autograd.grad(y, [xr] + list(block.parameters()), torch.ones_like(y) * 0.37)
-    return [y] + list(g)
+    ps = [xr] + list(block.parameters())
+    g = torch.autograd.grad(y, ps, torch.ones_like(y) * 0.37, allow_unused=True)      # unused: a convolution bias in front of a CIN
+    return [y] + [torch.zeros_like(p) if gi is None else gi for p, gi in zip(ps, g)]  # (cin.conv_before_film), reference gradient = noise
 
 torch.manual_seed(3)
 kw = dict(is_time=True, nl_dim=[2, 3], batch_norm=False)
@@ -58,10 +59,13 @@ assert r_ops.get_plugin is not orig[0] and R.FILM.forward is cno.cin.film_forwar
 assert R.CNOBlock.forward is not orig[2] and R.ResidualBlock.forward is not orig[3]
 after = [run(b, x, t) for b, x in zip(blocks, xs)]
 for bs, as_ in zip(before, after):
+    # a convolution bias in front of an instance norm has a zero gradient (round-off noise in the reference, exactly zero after
+    # the patch): errors are measured against the block's gradient scale, not against each tensor's own maximum
+    floor = 1e-3 * max(float(u.detach().abs().max()) for u in bs[1:])
     for u, v in zip(bs, as_):
         assert u.shape == v.shape
-        err = float((u - v).abs().max() / u.abs().max().clamp_min(1e-30))
-        assert err < 1e-5, err
+        err = float((u - v).abs().max()) / max(float(u.abs().max()), floor)
+        assert err < 1e-4, err      # 1e-7 rounding differences of the bias-free convolution + leaky-ReLU kinks (tests/test_cno_model.py)
 # flavours the patch does not cover run the reference's own forward
 bn = R.CNOBlock(3, 4, 16, 16, is_time=False, nl_dim=[2, 3], batch_norm=True)
 y = bn(xs[0], t)
@@ -186,7 +190,9 @@ def test_patch_reference_standin_gpu():
             xr = x.clone().requires_grad_(True)
             y = b(xr, t)
             dy = torch.linspace(-1, 1, y.numel(), device='cuda').reshape(y.shape)
-            return y, [y] + list(torch.autograd.grad(y, [xr] + list(b.parameters()), dy))
+            ps = [xr] + list(b.parameters())
+            gs = torch.autograd.grad(y, ps, dy, allow_unused=True)       # unused: a convolution bias in front of a CIN (cin.conv_before_film)
+            return y, [y] + [torch.zeros_like(p) if gi is None else gi for p, gi in zip(ps, gs)]
         before = [run(b, x)[1] for b, x in zip(blocks, xs)]
         assert cno.patch_reference()
         for n in ('bias_act', 'upfirdn2d', 'filtered_lrelu'):
