@@ -4,6 +4,7 @@
 one kernel pass (csrc/cin.cu), with a fused backward.  `film_forward` is a drop-in for `FILM.forward`
 that keeps the module's parameters / state_dict untouched; the four tiny Linear layers stay in torch
 (autograd carries dscale / dshift into them)."""
+import contextlib
 import ctypes
 import os
 import torch
@@ -113,6 +114,20 @@ def _film_params(t, gamma, beta, w1s, b1s, W2s, b2s, w1b, b1b, W2b, b2b, n, c):
     return t32, P, lat
 
 
+# Parameter-gradient side stream (opt-in, set by train.Trainer): cno_film_bwd_finish turns the [N, C] sums of a FILM backward into
+# the module's ten parameter gradients.  Nothing in backward consumes them, yet at 8.7 us of dependent L2 round trips x 97 modules
+# they are 0.85 ms on the critical path of the training step.  With a side stream they run next to the remaining backward (the
+# launch occupies 6-36 CTAs); the consumer (bucket gather / optimiser) joins with join_param_grad_stream().  None: same stream.
+PARAM_GRAD_STREAM = None
+_side_keepalive = []          # buffers read / written on the side stream, kept until the join (no allocator reuse under a running kernel)
+
+
+def join_param_grad_stream():
+    if PARAM_GRAD_STREAM is not None and _side_keepalive:
+        torch.cuda.current_stream(PARAM_GRAD_STREAM.device).wait_stream(PARAM_GRAD_STREAM)
+        _side_keepalive.clear()
+
+
 def _film_backward(saved, dy, meta):
     """dx and the ten parameter gradients of one FILM module from (x, t, scale, mean, rstd, weights) and d(FILM output):
     cno_cin_bwd + cno_film_bwd_finish."""
@@ -130,10 +145,15 @@ def _film_backward(saved, dy, meta):
         sizes = [c, c, lat, lat, c * lat, c, lat, lat, c * lat, c]      # dgamma dbeta dw1s db1s dW2s db2s dw1b db1b dW2b db2b
         flat = torch.empty([sum(sizes)], dtype=torch.float32, device=x.device)
         g = list(flat.split(sizes))
-        rc = lib.cno_film_bwd_finish(_ptr(s12[0]), _ptr(s12[1]), _ptr(t32), _ptr(gamma), _ptr(beta), _ptr(scale),
-                                     _ptr(w1s), _ptr(b1s), _ptr(W2s), _ptr(w1b), _ptr(b1b), _ptr(W2b),
-                                     _ptr(g[0]), _ptr(g[1]), _ptr(g[4]), _ptr(g[5]), _ptr(g[2]), _ptr(g[3]),
-                                     _ptr(g[8]), _ptr(g[9]), _ptr(g[6]), _ptr(g[7]), n, c, lat, _stream(x))
+        side = PARAM_GRAD_STREAM if (PARAM_GRAD_STREAM is not None and PARAM_GRAD_STREAM.device == x.device) else None
+        if side is not None:
+            side.wait_stream(torch.cuda.current_stream(x.device))       # the sums of cno_cin_bwd
+            _side_keepalive.append((s12, flat, saved))
+        with (torch.cuda.stream(side) if side is not None else contextlib.nullcontext()):
+            rc = lib.cno_film_bwd_finish(_ptr(s12[0]), _ptr(s12[1]), _ptr(t32), _ptr(gamma), _ptr(beta), _ptr(scale),
+                                         _ptr(w1s), _ptr(b1s), _ptr(W2s), _ptr(w1b), _ptr(b1b), _ptr(W2b),
+                                         _ptr(g[0]), _ptr(g[1]), _ptr(g[4]), _ptr(g[5]), _ptr(g[2]), _ptr(g[3]),
+                                         _ptr(g[8]), _ptr(g[9]), _ptr(g[6]), _ptr(g[7]), n, c, lat, _stream(x))
         _lib.check(rc, 'film_bwd_finish')
     return dx, [gi.view(shape).to(dt) for gi, (dt, shape) in zip(g, meta)]
 

@@ -102,7 +102,7 @@ class Trainer:
     `graph=True` the whole step (forward, backward, bucket copies + all-reduces on the forked stream, AdamW) replays as one
     CUDA graph per rank.  `mode='finetune'`: CNO_FineTune.py workload (finetune.initialize_FT wrappers, three AdamW groups)."""
 
-    def __init__(self, cfg=None, device='cuda', ddp=False, graph=False, autocast=None, buckets=4, mode='train', ft=None):
+    def __init__(self, cfg=None, device='cuda', ddp=False, graph=False, autocast=None, buckets=4, mode='train', ft=None, side_stream=True):
         self.device = torch.device(device)
         if mode == 'finetune':
             from . import finetune
@@ -150,6 +150,13 @@ class Trainer:
             groups, wd = [{'params': self.params, 'lr': self.model.lr}], self.model.weight_decay
         self.opt = torch.optim.AdamW(groups, lr=self.model.lr, weight_decay=wd, capturable=bool(graph and self.device.type == 'cuda'),
                                      **(dict(fused=True) if self.device.type == 'cuda' else {}))    # one multi-tensor kernel family
+        # FILM parameter gradients on a side stream (cin.PARAM_GRAD_STREAM): joined before they are gathered / used by AdamW
+        self._side = None
+        if self.device.type == 'cuda' and side_stream:
+            from . import cin as _cin
+            if _cin.PARAM_GRAD_STREAM is None or _cin.PARAM_GRAD_STREAM.device != self.device:
+                _cin.PARAM_GRAD_STREAM = torch.cuda.Stream(self.device)
+            self._side = _cin
         self.autocast = autocast
         self.graph = None
         self.use_graph = bool(graph) and self.device.type == 'cuda'
@@ -159,6 +166,8 @@ class Trainer:
     def _launch_bucket(self, b):
         start, end, members = self.buckets[b]
         self._launched[b] = True
+        if self._side is not None:
+            self._side.join_param_grad_stream()
         have = [p for p in members if p.grad is not None]
         if len(have) < len(members):                   # a parameter without a gradient this step contributes zeros
             self.flat_grad[start:end].zero_()
@@ -204,6 +213,8 @@ class Trainer:
             pred = self.model(x, t)
         loss = self.model.training_loss(pred.float(), y.float())
         loss.backward()
+        if self._side is not None:
+            self._side.join_param_grad_stream()
         if self.world > 1:
             self._finish_allreduce()
         self.opt.step()
@@ -236,6 +247,10 @@ class Trainer:
         self.graph = None
         self.static = None
         self.static_loss = None
+        if self._side is not None:
+            self._side.PARAM_GRAD_STREAM = None
+            self._side._side_keepalive.clear()
+            self._side = None
         if self.device.type == 'cuda':
             torch.cuda.synchronize(self.device)
 
