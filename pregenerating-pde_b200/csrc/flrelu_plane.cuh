@@ -56,7 +56,7 @@ static inline int make_geom(Geom& g, const Plan& plan, int rs_unused = 0) {
     g.UWp = 4 * p.G;
     // up-res planes of at most 64 columns (8^2 / 16^2 inputs of the I configuration, 16 -> 8 of D, 8 -> 16 of U): measured 1.3-1.9x over
     // the streaming kernel; at 32^2 (80 columns, 22 KB of shared memory per plane = 10 planes per SM) the two are equal
-    if (g.UWp > 64 || p.H > 64 || p.W > 64) return -1;
+    if (g.UWp > 96 || p.H > 64 || p.W > 64) return -1;          // 65..96 columns: only when all planes are resident at once, see below
     g.nbodies = (p.OH + 5 + ko - 1) / ko;
     g.SR = g.nbodies * pb;
     (void)pq; (void)wly;
@@ -78,6 +78,10 @@ static inline int make_geom(Geom& g, const Plan& plan, int rs_unused = 0) {
     int per_sm = (int)((220 * 1024) / per);
     if (per_sm > 2048 / g.UWp) per_sm = 2048 / g.UWp;
     if (per_sm < 1) return -1;
+    // 80-96 columns (32^2 inputs): 22 KB per plane = 10 planes per SM.  When the tensor fits the machine in one wave the kernel is one
+    // plane latency (12-14 us, against a 20 us floor of the streaming kernel's 12-row bodies on short planes, which is slower than
+    // the reference's kernel on [32,16,32,32]); with more planes than that the second wave ties it with the streaming kernel
+    if (g.UWp > 64 && (long long)p.NC > (long long)per_sm * 148) return -1;
     int P = (96 + g.UWp - 1) / g.UWp;                           // >= 96 threads: small CTAs, many per SM, short tail
     if (P > per_sm) P = per_sm;
     if (P > p.NC) P = p.NC;
