@@ -387,6 +387,59 @@ def measure_train(args, world, rank, dev, mode='train'):
     return rec
 
 
+def run_cno_rollout(args):
+    """Forward-only autoregressive rollout of TestCNO_ALL.py:124-188 (`pred = model(inp, t)`; `inp[:, :dim] = pred`), K = 7 steps of
+    the TrainCNO_time_L model captured as ONE CUDA graph under no_grad (SIGN_NONE launches: no sign masks are written);
+    value = model evaluations per second (samples x rollout steps)."""
+    import pregenerating_pde_b200 as cno
+    torch.cuda.set_device(0)
+    dev = torch.device('cuda', 0)
+    torch.backends.cudnn.benchmark = True
+    model = cno.cno_model.CNO_time(**cno.cno_model.train_config_L()).to(dev).eval()
+    B, K = args.batch, 7
+    t, x, _ = cno.train.synthetic_fpo_batch(B, device=dev, seed=1)
+    hx = x.cpu().pin_memory()
+
+    def rollout(inp):
+        outs = []
+        for _ in range(K):
+            pred = model(inp, t)
+            inp = torch.cat([pred, inp[:, pred.shape[1]:]], 1)
+            outs.append(pred)
+        return torch.stack(outs)
+    with torch.no_grad():
+        side = torch.cuda.Stream(); side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                rollout(x)
+        torch.cuda.current_stream().wait_stream(side)
+        static_x = x.clone()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            out = rollout(static_x)
+        for _ in range(max(args.warmup, 3)):
+            g.replay()
+        sampler = ClockSampler(0); sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); e0.record()
+        for _ in range(args.steps):
+            g.replay()
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / args.steps
+        t0 = time.perf_counter()
+        for _ in range(args.steps):                       # e2e: initial condition from pinned host memory, last prediction's mean read back
+            static_x.copy_(hx, non_blocking=True); g.replay(); v = float(out[-1].mean())
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+        clocks = sampler.stop()
+    print(json.dumps({'metric': 'cno_rollout_model_evaluations_per_s', 'value': round(B * K / (ms * 1e-3), 1), 'unit': 'samples*steps/s', 'n_gpus': 1,
+                      'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': round(ms, 3), 'higher_is_better': True, 'scaling': 'weak',
+                      'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+                      'config': {'workload': f'CNO_time TrainCNO_time_L model, no_grad autoregressive rollout of {K} steps (TestCNO_ALL.py:124-188), batch {B}, one CUDA graph',
+                                 'rollout_steps': K, 'batch': B},
+                      'e2e': {'value': round(B * K / (e2e_ms * 1e-3), 1), 'unit': 'samples*steps/s', 'h2d_bytes_per_step': hx.numel() * 4, 'd2h_bytes_per_step': 4,
+                              'ms_per_step': round(e2e_ms, 3)}, 'clocks': clocks}), flush=True)
+
+
 def run_cno_train(args, mode='train'):
     """Secondary workloads: `--workload cno_train` (BASELINE.json configs[2], [3]) and `--workload cno_finetune` (configs[4]) as
     the headline of their own JSON line; value = samples/s over all GPUs."""
@@ -404,7 +457,7 @@ def run_cno_train(args, mode='train'):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument('--workload', default='flr', choices=['flr', 'cno_train', 'cno_finetune'])
+    ap.add_argument('--workload', default='flr', choices=['flr', 'cno_train', 'cno_finetune', 'cno_rollout'])
     ap.add_argument('--autocast', default='none', choices=['none', 'bf16'])
     ap.add_argument('--no-train', dest='no_train', action='store_true', help='flr workload: skip the cno_train sub-record')
     ap.add_argument('--batch', type=int, default=32)
@@ -422,6 +475,8 @@ def main():
         return run_reference_arm(args)
     if args.workload == 'cno_train':
         return run_cno_train(args)
+    if args.workload == 'cno_rollout':
+        return run_cno_rollout(args)
     if args.workload == 'cno_finetune':
         if args.batch == 32 and args.autocast == 'none':
             args.autocast = 'bf16'                     # BASELINE.json configs[4]: bf16

@@ -557,6 +557,56 @@ def test_cin_residual_epilogue(cno, N, C, S, dtype):
     for a, r in zip(gm, gm_ref):
         assert rel(a, r) < (1e-4 if dtype == torch.float32 else 4e-2)
 @pytest.mark.gpu
+@pytest.mark.parametrize('N,C,S,pair', [(4, 16, 128, False), (8, 64, 32, False), (32, 256, 8, False), (2, 8, 256, False),
+                                        (2, 6, 64, True), (2, 3, 128, True), (8, 40, 8, True)])
+def test_film_accuracy_against_fp64_floor(cno, N, C, S, pair):
+    """Where the fp32 limits of the CIN tests come from (2e-5 / 1e-4 / 3e-5 / 2e-4 instead of 1e-5 need a measured
+    floor).  Truth = the eager FILM module (and, for `pair`, the oracle's filtered_lrelu behind it) evaluated in fp64.  Two fp32
+    evaluations are measured against it: the module's own torch ops on the CPU (what every other CIN test uses as reference) and
+    our kernels.  The gradients with respect to gamma / beta / the Linear weights are sums over N*H*W of products with heavy
+    cancellation: the reference's own fp32 evaluation sits 1e-6 .. 1e-4 from the fp64 truth there.  Required: our error <=
+    max(1e-5, 3 x the reference fp32 error) for every quantity; both errors go to the parity report."""
+    from pregenerating_pde_b200 import cno_model
+    import copy
+    torch.manual_seed(7 * N + C + S)
+    film = cno_model.FILM(C, dim=[2, 3], s=S)
+    act = cno_model.LReLu(C, C, S, S, **cno_model._filter_args(S, S, 2.0001, 0.8))
+    with torch.no_grad():
+        for p_ in list(film.parameters()) + [act.bias]:
+            p_.add_(0.3 * torch.randn_like(p_))
+    x = torch.randn(N, C, S, S) * 1.3 + 0.2
+    t = torch.rand(N)
+
+    def run(f, a, xx, tt, dd, fmod=None):
+        fmod = fmod if fmod is not None else f
+        xr = xx.clone().requires_grad_(True)
+        z = f(xr, tt)
+        if pair:
+            z = O.filtered_lrelu(z, a.up_filter.to(z.dtype), a.down_filter.to(z.dtype), a.bias, up=a.up_factor, down=a.down_factor,
+                                 padding=a.padding, gain=math.sqrt(2), slope=0.2)
+        ps = list(fmod.parameters()) + ([a.bias] if pair else [])
+        return z, torch.autograd.grad(z, [xr] + ps, dd if dd is not None else torch.ones_like(z))
+    y32, _ = run(film, act, x, t, None)
+    dy = torch.randn_like(y32)
+    y32, g32 = run(film, act, x, t, dy)
+    f64, a64 = copy.deepcopy(film).double(), copy.deepcopy(act).double()
+    _eager = lambda self, xx, tt: (self.norm(xx) * self.lat2scale(self.inp2lat_sacale(tt.reshape(-1, 1))).unsqueeze(2).unsqueeze(3)
+                                   + self.lat2bias(self.inp2lat_bias(tt.reshape(-1, 1))).unsqueeze(2).unsqueeze(3))
+    y64, g64 = run(lambda xx, tt: _eager(f64, xx, tt), a64, x.double(), t.double(), dy.double(), fmod=f64)
+    fg, ag = copy.deepcopy(film).to(DEV), copy.deepcopy(act).to(DEV)
+    xg = x.to(DEV).requires_grad_(True)
+    yg = cno.cin.film_lrelu(fg, ag, xg, t.to(DEV)) if pair else fg(xg, t.to(DEV))
+    gg = torch.autograd.grad(yg, [xg] + list(fg.parameters()) + ([ag.bias] if pair else []), dy.to(DEV))
+    names = ['y', 'dx'] + ['d' + n for n, _ in film.named_parameters()] + (['dlrelu.bias'] if pair else [])
+    row = dict(case=f'[{N},{C},{S},{S}]' + (' FILM -> filtered_lrelu pair' if pair else ' FILM'))
+    for nm, ours, ref32, truth in zip(names, [yg] + list(gg), [y32] + list(g32), [y64] + list(g64)):
+        e_ours, e_ref = rel(ours, truth), rel(ref32, truth)
+        row[nm] = dict(ours=e_ours, reference_fp32=e_ref)
+        assert e_ours <= max(1e-5, 3 * e_ref), (nm, e_ours, e_ref)
+    report('film_accuracy_vs_fp64', row)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize('s_in,s_out,N,C', [(16, 16, 2, 3), (32, 16, 3, 5), (16, 32, 2, 4), (64, 64, 2, 6), (128, 128, 2, 3), (8, 8, 32, 40)])
 def test_film_lrelu_prologue_fusion(cno, s_in, s_out, N, C, monkeypatch):
     """LReLu(FILM(x, t)) with the CIN affine applied inside the filtered_lrelu kernel (cno_film_stats +
