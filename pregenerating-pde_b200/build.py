@@ -13,7 +13,8 @@ OBJ = os.path.join(os.path.dirname(HERE), 'build', 'cno_b200')
 LIB = os.path.join(HERE, 'libcno_b200.so')
 SOURCES = ['capi.cu', 'bias_act.cu', 'upfirdn2d.cu', 'flrelu_act.cu', 'cin.cu', 'flrelu_fused.cu',
            'flrelu_fused_f32.cu', 'flrelu_fused_bf16.cu', 'flrelu_fused_f16.cu',
-           'flrelu_plane_f32.cu', 'flrelu_plane_bf16.cu', 'flrelu_plane_f16.cu']
+           'flrelu_plane_f32.cu', 'flrelu_plane_bf16.cu', 'flrelu_plane_f16.cu'] + \
+          [f'flrelu_fused_{t}_p{i}.cu' for t in ('f32', 'bf16', 'f16') for i in range(5)]
 NVCC_FLAGS = ['-std=c++17', '-O3', '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo',
               '-Xcompiler', '-fPIC', '--threads', '2']
 
@@ -43,11 +44,13 @@ def compile_one(src, force, extra):
 def build(force=False, quick=False, verbose=True):
     os.makedirs(OBJ, exist_ok=True)
     extra = ['-DFLR_QUICK'] if quick else []
+    sources = [s for s in SOURCES if not (quick and '_p' in s and s.startswith('flrelu_fused_'))]
+    sources.sort(key=lambda s: 0 if '_p' in s else 1)          # the long compilations first
     stamp = os.path.join(OBJ, 'quick.stamp')
     if quick != os.path.exists(stamp):
         force = True
     with concurrent.futures.ThreadPoolExecutor(max_workers=min(len(SOURCES), os.cpu_count() or 4)) as ex:
-        results = list(ex.map(lambda s: compile_one(s, force, extra), SOURCES))
+        results = list(ex.map(lambda s: compile_one(s, force, extra), sources))
     if quick:
         open(stamp, 'w').close()
     elif os.path.exists(stamp):

@@ -1,0 +1,4 @@
+// fused filtered_lrelu kernels, float storage, part 2 of 5 (flrelu_fused_parts.cuh)
+#define FLR_PART 2
+#define FLR_TYPE float
+#include "flrelu_fused_parts.cuh"

@@ -299,6 +299,17 @@ int launch_mode(const Plan& plan, const CUtensorMap& map, int mode, cudaStream_t
     return launch_variant<T, C, SIGN_NONE>(plan, map, st);
 }
 
+// The kernels of one storage type are spread over five translation units (flrelu_fused_parts.cuh: FLR_PART 0..4) so that the
+// library builds in a few minutes on 8 cores; the unit that holds launch_cfg<T> only sees declarations.
+#ifndef FLR_QUICK
+#define FLR_EXTERN_MODE(T, U, D, R) extern template int launch_mode<T, Cfg<U, D, R, R>>(const Plan&, const CUtensorMap&, int, cudaStream_t);
+#define FLR_EXTERN_ALL(T) FLR_EXTERN_MODE(T, 2, 2, 0) FLR_EXTERN_MODE(T, 2, 2, 1) FLR_EXTERN_MODE(T, 2, 4, 0) FLR_EXTERN_MODE(T, 2, 4, 1) \
+    FLR_EXTERN_MODE(T, 4, 2, 0) FLR_EXTERN_MODE(T, 4, 2, 1) FLR_EXTERN_MODE(T, 4, 2, 2) FLR_EXTERN_MODE(T, 4, 2, 3)
+#ifndef FLR_PART
+FLR_EXTERN_ALL(float) FLR_EXTERN_ALL(__nv_bfloat16) FLR_EXTERN_ALL(__half)
+#endif
+#endif
+
 template <class T>
 int launch_cfg(const Plan& plan, const CUtensorMap& map, int mode, cudaStream_t st) {
 #define V(U, D, R) if (plan.up == U && plan.down == D && plan.rx == R && plan.ry == R) return launch_mode<T, Cfg<U, D, R, R>>(plan, map, mode, st);
