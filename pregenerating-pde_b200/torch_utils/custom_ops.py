@@ -193,7 +193,7 @@ class _FilteredLReluPlugin:
             raise RuntimeError('x is empty')
         if fu.ndim not in (1, 2) or fd.ndim not in (1, 2) or fu.numel() == 0 or fd.numel() == 0:
             raise RuntimeError('fu and fd must be non-empty and rank 1 or 2')
-        if b.ndim != 1 or b.shape[0] != x.shape[1]:
+        if b.ndim != 1 or (b.shape[0] != x.shape[1] and b.numel() != 0):      # empty b (extension): no bias, NULL goes to the kernel
             raise RuntimeError('b must be a vector with the same number of channels as x')
         if up < 1 or down < 1:
             raise RuntimeError('up and down must be at least 1')

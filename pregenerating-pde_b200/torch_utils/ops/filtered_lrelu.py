@@ -105,8 +105,9 @@ class _FilteredLRelu(torch.autograd.Function):
             fd = fd.square()[None]
         if si is None:
             si = torch.empty([0])
-        if b is None:
-            b = torch.zeros([x.shape[1]], dtype=x.dtype, device=x.device)
+        no_bias = b is None
+        if no_bias:
+            b = torch.empty([0], dtype=x.dtype, device=x.device)      # plugin extension: empty = no bias (no zero-fill launch per backward)
         strides = [x.stride(i) for i in range(x.ndim) if x.size(i) > 1]
         if any(a < c for a, c in zip(strides[:-1], strides[1:])):
             warnings.warn('low-performance memory layout detected in filtered_lrelu input', RuntimeWarning)
@@ -118,7 +119,7 @@ class _FilteredLRelu(torch.autograd.Function):
                                                clamp, flip, write_signs, db=db, signs_only=signs_only)
         if rc < 0:
             # generic composition on our own kernels; keeps only the bit-packed mask (filtered_lrelu.py:215-221)
-            y = x.add(b.unsqueeze(-1).unsqueeze(-1))
+            y = x.clone() if no_bias else x.add(b.unsqueeze(-1).unsqueeze(-1))
             y = upfirdn2d.upfirdn2d(x=y, f=fu, up=up, padding=[px0, px1, py0, py1], gain=up ** 2, flip_filter=flip)
             so = _plugin.filtered_lrelu_act_(y, si, sx, sy, gain, slope, clamp, write_signs)
             y = upfirdn2d.upfirdn2d(x=y, f=fd, down=down, flip_filter=flip)
