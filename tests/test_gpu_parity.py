@@ -151,6 +151,42 @@ def test_filtered_lrelu_small_planes_both_kernels(cno, name, s_in, s_out, N, C, 
     assert torch.equal(out[1][3][..., swv // 4 + 1:], out[0][3][..., swv // 4 + 1:])       # row padding bytes: zero from both
 
 
+RAGGED = [(12, 20, None, 2, 5), (20, 12, None, 3, 3), (24, 8, None, 1, 7), (40, 100, None, 2, 3), (100, 36, None, 1, 4),
+          (16, 16, [9, 10, 13, 10], 2, 3), (16, 24, [11, 8, 9, 10], 2, 3), (64, 128, [11, 10, 11, 10], 1, 3)]
+
+
+@pytest.mark.parametrize('kernel', ['plane', 'streaming'])
+@pytest.mark.parametrize('h,w,pad,N,C', RAGGED)
+def test_filtered_lrelu_ragged_shapes(cno, h, w, pad, N, C, kernel):
+    """Rectangular planes and asymmetric paddings (px0 != py0: no fused variant, the call must fall through to the generic
+    composition and still agree) through the same entry point with either fused kernel enabled."""
+    cfg = dict(O.lrelu_config(16, 16))
+    if pad is not None:
+        cfg['padding'] = pad
+    g = torch.Generator().manual_seed(7 * h + w + C)
+    x, b = torch.randn(N, C, h, w, generator=g), torch.randn(C, generator=g)
+    xr, br = x.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    y_ref = O.filtered_lrelu(xr, cfg['fu'], cfg['fd'], br, up=cfg['up'], down=cfg['down'], padding=cfg['padding'])
+    dy = torch.randn(y_ref.shape, generator=g)
+    dx_ref, db_ref = torch.autograd.grad(y_ref, [xr, br], dy)
+    lib = cno._lib.load()
+    prev = lib.cno_filtered_lrelu_plane_kernel(-1)
+    try:
+        lib.cno_filtered_lrelu_plane_kernel(1 if kernel == 'plane' else 0)
+        y, dx, db, mask = fl_case(cno, x, b, dy, cfg)
+    finally:
+        lib.cno_filtered_lrelu_plane_kernel(prev)
+    assert y.shape == y_ref.shape and dx.shape == x.shape
+    errs = (rel(y, y_ref), rel(dx, dx_ref), rel(db, db_ref))
+    assert max(errs) < 1e-5, errs
+    if mask is not None and mask.dtype == torch.uint8 and mask.dim() == 4:
+        v = O.filtered_lrelu_preact(x, cfg['fu'], b, up=cfg['up'], padding=cfg['padding'])
+        sh, swb, swv = O.sign_mask_shape(y.shape[2:], cfg['fd'], cfg['down'])
+        if tuple(mask.shape[2:]) == (sh, swb):
+            bad = O.unpack_sign_mask(mask.cpu(), swv) != O.sign_mask_from_preact(v, 0.2, math.sqrt(2), None, sh, swv)
+            assert int((bad & (v[:, :, :sh, :swv].abs() > 1e-5)).sum()) == 0
+
+
 def test_filtered_lrelu_generic_golden(cno, golden):
     """clamp + flip + 8-tap filters: no fused variant -> generic composition on our kernels."""
     g = golden['filtered_lrelu']
