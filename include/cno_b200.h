@@ -145,6 +145,17 @@ int cno_film_bwd_finish(const float* s1, const float* s2, const float* t, const 
                         float* dgamma, float* dbeta, float* dW2s, float* db2s, float* dw1s, float* db1s,
                         float* dW2b, float* db2b, float* dw1b, float* db1b, int n, int c, int lat, void* stream);
 
+/* Allocation-free CIN forward.  No counterpart in the reference: added for callers that
+ * cannot allocate device memory (stream capture, tight serving loops, harnesses that forbid cudaMalloc).  Same result as
+ * cno_cin_fwd; the per-plane statistics that cno_cin_fwd leaves in the caller's mean / rstd buffers live in a fixed array inside
+ * the library's device image (512 KB per GPU that loads the library, held until the process exits), so the call allocates
+ * nothing and the statistics are not returned (forward only: no backward can follow it).
+ * Limit: n * c <= 65536 planes, otherwise cudaErrorInvalidValue with a message in cno_last_error().
+ * The array is shared by every call on a device and keeps the last call's contents (nothing in it needs clearing: every entry is
+ * written before it is read within a launch); calls that overlap on the GPU -- different streams with no dependency -- race. */
+int cno_cin_fwd_noalloc(const void* x, void* y, const float* gamma, const float* beta, const float* scale,
+                        const float* shift, int dtype, int n, int c, int hw, float eps, void* stream);
+
 /* Measurement helper used by bench.py / tests (not part of the reference surface): FP32 FMA issue
  * rate probe.  variant 0 = scalar FFMA, 1 = packed fma.rn.f32x2.  Writes elapsed-cycle-independent
  * results to out[threads]; returns 0. */

@@ -671,6 +671,53 @@ extern "C" int cno_cin_fwd_res(const void* x, const void* residual, void* y, con
     return cin_dispatch<false>(p, dtype, (cudaStream_t)stream);
 }
 
+// ---- allocation-free CIN forward -----------------------------------------------------------------------------------------------
+// cno_cin_fwd leaves the per-plane statistics (mean, rstd: 2 x N*C floats) in caller memory: the streaming kernel and the
+// statistics kernel write them and read them back, and the backward wants them.  A forward-only caller (inference, a serving
+// loop, code under stream capture) has no use for them and may not be able to allocate them.  This variant keeps them in a
+// fixed array that lives in the library's device image: every GPU that loads the library holds CIN_NOALLOC_BYTES of it until the
+// process exits.  Nothing in it has to start at zero (each plane's two entries are written before they are read in the same
+// launch), so it is never cleared and always holds the previous call's statistics.  All calls on one device share it: two calls
+// that overlap on the GPU (different streams, no dependency between them) race on it.
+constexpr int CIN_NOALLOC_MAX_PLANES = 65536;                                   // N * C of one call
+constexpr size_t CIN_NOALLOC_BYTES = 2 * sizeof(float) * (size_t)CIN_NOALLOC_MAX_PLANES;   // 512 KB
+static __device__ __align__(256) float g_cin_noalloc_stats[2 * CIN_NOALLOC_MAX_PLANES];
+
+// device address of the array on the CURRENT device (host code cannot use the symbol itself as a pointer), looked up once per device
+static int cin_noalloc_scratch(float** out) {
+    static std::atomic<float*> addr[CNO_MAX_DEVICES];
+    int d = -1;
+    cudaError_t e = cudaGetDevice(&d);
+    if (e != cudaSuccess) { cno_set_error("cin_fwd_noalloc: cudaGetDevice failed: %s", cudaGetErrorString(e)); return (int)e; }
+    const bool cached = d >= 0 && d < CNO_MAX_DEVICES;
+    float* ptr = cached ? addr[d].load(std::memory_order_acquire) : nullptr;
+    if (!ptr) {
+        e = cudaGetSymbolAddress((void**)&ptr, g_cin_noalloc_stats);
+        if (e != cudaSuccess || !ptr) {
+            cno_set_error("cin_fwd_noalloc: cudaGetSymbolAddress(statistics scratch) failed on device %d: %s", d, cudaGetErrorString(e));
+            return e != cudaSuccess ? (int)e : (int)cudaErrorInvalidSymbol;
+        }
+        if (cached) addr[d].store(ptr, std::memory_order_release);
+    }
+    *out = ptr;
+    return 0;
+}
+
+extern "C" int cno_cin_fwd_noalloc(const void* x, void* y, const float* gamma, const float* beta, const float* scale,
+                                   const float* shift, int dtype, int n, int c, int hw, float eps, void* stream) {
+    CNO_CHECK_ARG(x && y && gamma && beta && scale && shift, "cin_fwd_noalloc: null pointer");
+    CNO_CHECK_ARG(n >= 0 && c > 0 && hw > 0, "cin_fwd_noalloc: bad sizes n=%d c=%d hw=%d", n, c, hw);
+    CNO_CHECK_ARG((int64_t)n * c <= CIN_NOALLOC_MAX_PLANES,
+                  "cin_fwd_noalloc: n*c = %lld planes exceed the built-in statistics scratch of %d planes (use cno_cin_fwd with caller buffers)",
+                  (long long)n * c, CIN_NOALLOC_MAX_PLANES);
+    if (n == 0) return 0;
+    float* stats = nullptr;
+    if (int rc = cin_noalloc_scratch(&stats)) return rc;
+    CinParams p{}; p.x = x; p.y = y; p.gamma = gamma; p.beta = beta; p.scale = scale; p.shift = shift;
+    p.mean = stats; p.rstd = stats + CIN_NOALLOC_MAX_PLANES; p.planes = (int64_t)n * c; p.c = c; p.hw = hw; p.eps = eps;
+    return cin_dispatch<false>(p, dtype, (cudaStream_t)stream);
+}
+
 extern "C" int cno_cin_bwd(const void* x, const void* dy, void* dx, const float* gamma, const float* scale,
                            const float* mean, const float* rstd, float* s1, float* s2, int dtype, int n, int c,
                            int hw, void* stream) {
