@@ -12,7 +12,7 @@
 //   MMA2  D[128 x 144] (TMEM) += A2[128 x 64] (constant band matrix of the 12-tap down filter, shifted by 32 rows per 64-row chunk)
 //                                * V chunk (two chunks per step)
 //   EPI2  once per half: tcgen05.ld of D, 12-tap horizontal down-FIR in registers (a thread owns one output row), bf16 -> y
-// Roles: warps 0-7 epilogue (TMEM lane quarter = warp & 3, column group = warp >> 2), warp 8 lane 0 issues every MMA, warp 9 lane 0
+// Roles: warps 0-7 epilogue (TMEM lane quarter = warp & 3, column group = warp >> 2), warp 8 lane 0 issues MMA1, warp 10 lane 0 MMA2, warp 9 lane 0
 // loads AH with cp.async.bulk.  U and V are double-buffered, so MMA1 of step g + 1 and MMA2 of step g run under EPI1.
 // Every mbarrier wait is bounded (a wrong descriptor must not hang the box): on a timeout all roles leave and err is set.
 // build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -o vbody_probe vbody_probe.cu
@@ -33,7 +33,7 @@ constexpr int V_BYTES = NG * 128 * 16;             // 36,864
 constexpr int A1_BYTES = 10 * 128 * 16, A2_BYTES = 8 * 256 * 16;
 constexpr int MASK_PITCH = 68;                     // bytes per mask row (272 columns / 4)
 constexpr int OFF_A1 = 0, OFF_A2 = OFF_A1 + A1_BYTES, OFF_AH = OFF_A2 + A2_BYTES, OFF_V = OFF_AH + 2 * AH_BYTES, OFF_END = OFF_V + 2 * V_BYTES;
-constexpr int NTHREADS = 320;
+constexpr int NTHREADS = 352;
 constexpr float SLOPE = 0.2f;
 
 __constant__ float c_wup[2][6];                    // vertical up-FIR taps per phase (gain folded in)
@@ -50,6 +50,10 @@ __device__ __forceinline__ void mma_bf16(uint32_t taddr, uint64_t adesc, uint64_
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
                  :: "r"(taddr), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+__device__ __forceinline__ void mma_bf16_ta(uint32_t taddr, uint32_t a_taddr, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                 :: "r"(taddr), "r"(a_taddr), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
 }
@@ -61,9 +65,17 @@ __device__ __forceinline__ bool bar_wait(uint64_t* bar, uint32_t parity, volatil
         uint32_t done;
         asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(a), "r"(parity) : "memory");
         if (done) return true;
-        if ((spin & 255) == 255 && (*abort || spin > (1u << 22))) { *abort = 1; return false; }
+        __nanosleep(40);                                // back off: a spinning lane takes issue slots from the epilogue warps of its scheduler
+        if ((spin & 255) == 255 && (*abort || spin > (1u << 20))) { *abort = 1; return false; }
     }
 }
+__device__ __forceinline__ bool warp_wait(uint64_t* bar, uint32_t parity, volatile int* abort, int lane) {
+    (void)lane;                                     // measured: lane 0 polling + shuffle is SLOWER (167 vs 139 us), every lane polls
+    const bool ok = bar_wait(bar, parity, abort);
+    return __all_sync(0xffffffffu, ok);
+}
+#define ST8(addr, r) asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" \
+    :: "r"(addr), "r"(r[0]),"r"(r[1]),"r"(r[2]),"r"(r[3]),"r"(r[4]),"r"(r[5]),"r"(r[6]),"r"(r[7]) : "memory")
 #define LD16(r, addr) asm volatile( \
     "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];" \
     : "=r"(r[0]),"=r"(r[1]),"=r"(r[2]),"=r"(r[3]),"=r"(r[4]),"=r"(r[5]),"=r"(r[6]),"=r"(r[7]),"=r"(r[8]),"=r"(r[9]),"=r"(r[10]),"=r"(r[11]),"=r"(r[12]),"=r"(r[13]),"=r"(r[14]),"=r"(r[15]) \
@@ -75,7 +87,10 @@ __device__ __forceinline__ bool bar_wait(uint64_t* bar, uint32_t parity, volatil
 struct Bars { uint64_t ah_full[2], ah_empty[2], u_full[2], u_empty[2], v_full[2], v_empty[2], d_full, d_empty; };
 
 __global__ void __launch_bounds__(NTHREADS, 1)
-vbody(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ y, uint8_t* __restrict__ mask, int* err, long long* cyc, int swapB) {
+vbody(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ y, uint8_t* __restrict__ mask, int* err, long long* cyc, int swapB, int mode, long long* tl) {
+    // tl: optional timeline of CTA 0, [step][8] clock64 stamps: 0 mma1 issue, 1 mma2 wait done, 2 mma2 issued, 3 epi u_full passed, 4 epi v_empty passed, 5 epi1 done, 6 epi2 done
+    // mode bit 3: input loaded once per CTA (every plane computes on the first one's rows), bit 4: A1 from tensor memory instead of shared memory
+    // mode bit 0: issue no MMA (commits only), bit 1: no EPI1 arithmetic / stores, bit 2: no EPI2 arithmetic / stores (timing ablations)
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ Bars bars;
     __shared__ uint32_t tmem_base;
@@ -113,24 +128,45 @@ vbody(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ y, uint8_t* __
     __syncthreads();
     FENCE_AFTER();
     volatile int* abort = &abort_flag;
+    constexpr uint32_t TA1 = 3 * NH;                                        // A1 in tensor memory: 128 lanes (rows) x 40 columns (two bf16 of K per column)
+    if (warp < 4) {
+        const int m = tid;                                                  // row of A1 = TMEM lane
+#pragma unroll
+        for (int j = 0; j < 5; j++) {
+            uint32_t w[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const int k0 = 16 * j + 2 * i, d0 = k0 - (m >> 1), d1 = d0 + 1;
+                __nv_bfloat162 hh = __floats2bfloat162_rn(d0 >= 0 && d0 < 6 ? c_wup[m & 1][d0] : 0.f, d1 >= 0 && d1 < 6 ? c_wup[m & 1][d1] : 0.f);
+                w[i] = *reinterpret_cast<uint32_t*>(&hh);
+            }
+            ST8(tmem_base + ((uint32_t)(32 * warp) << 16) + TA1 + 8 * j, w);
+        }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    }
+    FENCE_BEFORE();
+    __syncthreads();
+    FENCE_AFTER();
     const int nplanes = (PLANES - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
     const int G = nplanes * 6;                                              // steps: (plane, half, row tile)
     const uint32_t tU = tmem_base, tD = tmem_base + 2 * NH;                 // U0 | U1 | D, 144 columns each
     const uint32_t sA1 = smem_u32(smem + OFF_A1), sA2 = smem_u32(smem + OFF_A2), sAH = smem_u32(smem + OFF_AH), sV = smem_u32(smem + OFF_V);
 
-    if (warp == 8) {
+    if (warp == 8 || warp == 10) {
         if (lane == 0) {
             // D = F32, A = B = BF16, A K-major, B MN-major (bit 16), N = 144, M = 128
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 16) | ((uint32_t)(NH >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
             auto descB = [&](uint32_t addr, uint32_t group_stride) { return swapB ? make_desc(addr, group_stride, 128) : make_desc(addr, 128, group_stride); };
             auto mma1 = [&](int g) -> bool {
                 const int t = g % 3, hc = g / 3, h = hc & 1, pl = hc >> 1, b = g & 1;
-                if (t == 0 && !bar_wait(&bars.ah_full[h], pl & 1, abort)) return false;
+                if (t == 0 && (!(mode & 8) || pl == 0) && !bar_wait(&bars.ah_full[h], pl & 1, abort)) return false;
                 if (!bar_wait(&bars.u_empty[b], ((g >> 1) & 1) ^ 1, abort)) return false;
                 FENCE_AFTER();
+                if (tl && blockIdx.x == 0 && g < 64) tl[g * 8 + 0] = clock64() - t_start;
                 const int ks = t < 2 ? 5 : 1;
-                for (int s = 0; s < ks; s++)
-                    mma_bf16(tU + b * NH, make_desc(sA1 + s * 4096, 2048, 128), descB(sAH + h * AH_BYTES + (64 * t + 16 * s) * 16, KH * 16), idesc, s > 0);
+                if (!(mode & 1)) for (int s = 0; s < ks; s++)
+                    if (mode & 16) mma_bf16_ta(tU + b * NH, tmem_base + TA1 + 8 * s, descB(sAH + h * AH_BYTES + (64 * t + 16 * s) * 16, KH * 16), idesc, s > 0);
+                    else mma_bf16(tU + b * NH, make_desc(sA1 + s * 4096, 2048, 128), descB(sAH + h * AH_BYTES + (64 * t + 16 * s) * 16, KH * 16), idesc, s > 0);
                 mma_commit(&bars.u_full[b]);
                 if (t == 2) mma_commit(&bars.ah_empty[h]);
                 return true;
@@ -140,26 +176,28 @@ vbody(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ y, uint8_t* __
                 if (!bar_wait(&bars.v_full[b], (g >> 1) & 1, abort)) return false;
                 if (t == 0 && !bar_wait(&bars.d_empty, (hc & 1) ^ 1, abort)) return false;
                 FENCE_AFTER();
+                if (tl && blockIdx.x == 0 && g < 64) tl[g * 8 + 1] = clock64() - t_start;
                 const int c0 = 2 * t, c1 = t < 2 ? 2 * t + 1 : 2 * t;
-                for (int c = c0; c <= c1; c++) {
+                if (!(mode & 1)) for (int c = c0; c <= c1; c++) {
                     const int ks = c == 4 ? 1 : 4;
                     for (int s = 0; s < ks; s++)
                         mma_bf16(tD, make_desc(sA2 + (128 - 32 * c) * 16 + s * 8192, 4096, 128), descB(sV + b * V_BYTES + (64 * (c & 1) + 16 * s) * 16, 128 * 16),
                                  idesc, !(c == 0 && s == 0));
                 }
                 mma_commit(&bars.v_empty[b]);
+                if (tl && blockIdx.x == 0 && g < 64) tl[g * 8 + 2] = clock64() - t_start;
                 if (t == 2) mma_commit(&bars.d_full);
                 return true;
             };
-            bool ok = mma1(0);
-            for (int g = 0; g < G && ok; g++) {
-                if (g + 1 < G) ok = mma1(g + 1);
-                ok = ok && mma2(g);
-            }
+            // two issuing threads (measured: commit + wait + fence cost one thread ~ 450 cycles per group, ~ 1,000 per step when one thread
+            // issues both groups): warp 8 issues MMA1 (as far ahead as U allows: U[g & 1] is free once EPI1(g - 2) has LOADED it),
+            // warp 10 issues MMA2(g) when EPI1(g) has stored V
+            if (warp == 8) { bool ok = true; for (int g = 0; g < G && ok; g++) ok = mma1(g); }
+            else { bool ok = true; for (int g = 0; g < G && ok; g++) ok = mma2(g); }
         }
     } else if (warp == 9) {
         if (lane == 0) {
-            for (int i = 0; i < nplanes * 2; i++) {
+            for (int i = 0; i < ((mode & 8) ? 2 : nplanes * 2); i++) {
                 const int pl = i >> 1, h = i & 1, plane = (int)blockIdx.x + pl * (int)gridDim.x;
                 if (!bar_wait(&bars.ah_empty[h], (pl & 1) ^ 1, abort)) break;
                 const uint32_t bar = smem_u32(&bars.ah_full[h]);
@@ -178,33 +216,35 @@ vbody(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ y, uint8_t* __
         // EPI2: D of half hc -> horizontal down-FIR -> y
         auto depi = [&](int hc) -> bool {
             const int h = hc & 1, pl = hc >> 1, plane = (int)blockIdx.x + pl * (int)gridDim.x, o = 32 * q + lane;
-            if (!bar_wait(&bars.d_full, hc & 1, abort)) return false;
+            if (!warp_wait(&bars.d_full, hc & 1, abort, lane)) return false;
             FENCE_AFTER();
-            uint32_t cur[16], nxt[16];
             const int oc0 = 4 * cg;
-            LD16(cur, tD + lane_off + 16 * oc0);
-            TMEM_WAIT_LD();
+            if (!(mode & 4)) {
+                uint32_t d[5][16];                                     // column chunks oc0 .. oc0 + 4: one wait for all five loads
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-                const int oc = oc0 + k;
-                LD16(nxt, tD + lane_off + 16 * (oc + 1));
+                for (int k = 0; k < 5; k++) LD16(d[k], tD + lane_off + 16 * (oc0 + k));
                 TMEM_WAIT_LD();
-                uint32_t pk[4];
+                FENCE_BEFORE();
+                __syncwarp();
+                if (lane == 0) bar_arrive(&bars.d_empty);              // D is free again: the next half's MMA2 may start under the FIR below
 #pragma unroll
-                for (int i = 0; i < 8; i += 2) {
-                    float a0 = 0.f, a1 = 0.f;
+                for (int k = 0; k < 4; k++) {
+                    uint32_t pk[4];
 #pragma unroll
-                    for (int tt = 0; tt < 12; tt++) {
-                        const int j0 = 2 * i + tt, j1 = 2 * i + 2 + tt;
-                        a0 = fmaf(fd[tt], __uint_as_float(j0 < 16 ? cur[j0] : nxt[j0 - 16]), a0);
-                        a1 = fmaf(fd[tt], __uint_as_float(j1 < 16 ? cur[j1] : nxt[j1 - 16]), a1);
+                    for (int i = 0; i < 8; i += 2) {
+                        float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+                        for (int tt = 0; tt < 12; tt++) {
+                            const int j0 = 2 * i + tt, j1 = 2 * i + 2 + tt;
+                            a0 = fmaf(fd[tt], __uint_as_float(j0 < 16 ? d[k][j0] : d[k + 1][j0 - 16]), a0);
+                            a1 = fmaf(fd[tt], __uint_as_float(j1 < 16 ? d[k][j1] : d[k + 1][j1 - 16]), a1);
+                        }
+                        __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
+                        pk[i >> 1] = *reinterpret_cast<uint32_t*>(&hh);
                     }
-                    __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
-                    pk[i >> 1] = *reinterpret_cast<uint32_t*>(&hh);
+                    if (!(mode & 64) || pk[0] == 0x12345678u) *reinterpret_cast<uint4*>(y + ((size_t)plane * OH + o) * OW + 64 * h + 8 * (oc0 + k)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                 }
-                *reinterpret_cast<uint4*>(y + ((size_t)plane * OH + o) * OW + 64 * h + 8 * oc) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-#pragma unroll
-                for (int i = 0; i < 16; i++) cur[i] = nxt[i];
+                return true;
             }
             FENCE_BEFORE();
             __syncwarp();
@@ -214,38 +254,52 @@ vbody(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ y, uint8_t* __
         bool ok = true;
         for (int g = 0; g < G && ok; g++) {
             const int t = g % 3, hc = g / 3, h = hc & 1, pl = hc >> 1, b = g & 1, plane = (int)blockIdx.x + pl * (int)gridDim.x;
-            if (!bar_wait(&bars.u_full[b], (g >> 1) & 1, abort) || !bar_wait(&bars.v_empty[b], ((g >> 1) & 1) ^ 1, abort)) { ok = false; break; }
+            if (!warp_wait(&bars.u_full[b], (g >> 1) & 1, abort, lane)) { ok = false; break; }
+            if (tl && blockIdx.x == 0 && g < 64 && tid == 0) tl[g * 8 + 3] = clock64() - t_start;
             FENCE_AFTER();
-            if (t < 2 || q == 0) {
+            const bool active = (t < 2 || q == 0) && !(mode & 2);
+            const int ch0 = cg ? 5 : 0, nch = cg ? 4 : 5;
+            uint32_t rr[5][16];
+            if (active) {
+#pragma unroll
+                for (int k = 0; k < 5; k++) if (k < nch) LD16(rr[k], tU + b * NH + lane_off + 16 * (ch0 + k));
+                TMEM_WAIT_LD();
+            }
+            FENCE_BEFORE();
+            __syncwarp();
+            if (lane == 0) bar_arrive(&bars.u_empty[b]);              // U[b] is in registers: MMA1 of step g + 2 may overwrite it
+            if (!warp_wait(&bars.v_empty[b], ((g >> 1) & 1) ^ 1, abort, lane)) { ok = false; break; }
+            if (tl && blockIdx.x == 0 && g < 64 && tid == 0) tl[g * 8 + 4] = clock64() - t_start;
+            if (active) {
                 const int krow = 32 * q + lane, r = 128 * t + krow;
                 uint8_t* vdst = smem + OFF_V + b * V_BYTES + krow * 16;
                 uint8_t* mrow = mask + ((size_t)plane * UH + (r < UH ? r : 0)) * MASK_PITCH + 32 * h;
-                const int ch0 = cg ? 5 : 0, ch1 = cg ? 9 : 5;
-#pragma unroll 1
-                for (int ch = ch0; ch < ch1; ch++) {
-                    uint32_t rr[16];
-                    LD16(rr, tU + b * NH + lane_off + 16 * ch);
-                    TMEM_WAIT_LD();
-                    uint32_t bits = 0, pk[8];
 #pragma unroll
-                    for (int i = 15; i >= 0; i--) bits = __funnelshift_l(rr[i], bits, 2);        // (bits << 2) | top two bits of the value
+                for (int k = 0; k < 5; k++) if (k < nch) {
+                    const int ch = ch0 + k;
+                    uint32_t pk[8], bq[4] = {0, 0, 0, 0};                                          // four independent chains, one per mask byte
+#pragma unroll
+                    for (int i = 3; i >= 0; i--)
+#pragma unroll
+                        for (int j = 0; j < 4; j++) bq[j] = __funnelshift_l(rr[k][4 * j + i], bq[j], 2);   // (b << 2) | top two bits of the value
+                    const uint32_t bits = __byte_perm(__byte_perm(bq[0], bq[1], 0x0040), __byte_perm(bq[2], bq[3], 0x0040), 0x5410);
 #pragma unroll
                     for (int i = 0; i < 16; i += 2) {
-                        float a = __uint_as_float(rr[i]), c = __uint_as_float(rr[i + 1]);
+                        float a = __uint_as_float(rr[k][i]), c = __uint_as_float(rr[k][i + 1]);
                         a = fmaxf(a, SLOPE * a); c = fmaxf(c, SLOPE * c);
                         __nv_bfloat162 hh = __floats2bfloat162_rn(a, c);
                         pk[i >> 1] = *reinterpret_cast<uint32_t*>(&hh);
                     }
                     *reinterpret_cast<uint4*>(vdst + (2 * ch) * 2048) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                     *reinterpret_cast<uint4*>(vdst + (2 * ch + 1) * 2048) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-                    if (r < UH && !(h == 1 && ch == 0)) *reinterpret_cast<uint32_t*>(mrow + 4 * ch) = (bits >> 1) & 0x55555555u;   // code 1 = negative
+                    if (r < UH && !(h == 1 && ch == 0) && !(mode & 32)) *reinterpret_cast<uint32_t*>(mrow + 4 * ch) = (bits >> 1) & 0x55555555u;   // code 1 = negative
                 }
             }
-            FENCE_BEFORE();
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
-            if (lane == 0) { bar_arrive(&bars.u_empty[b]); bar_arrive(&bars.v_full[b]); }
-            if (t == 0 && g > 0) ok = depi(hc - 1);
+            if (lane == 0) bar_arrive(&bars.v_full[b]);
+            if (tl && blockIdx.x == 0 && g < 64 && tid == 0) tl[g * 8 + 5] = clock64() - t_start;
+            if (t == 0 && g > 0) { ok = depi(hc - 1); if (tl && blockIdx.x == 0 && g < 64 && tid == 0) tl[g * 8 + 6] = clock64() - t_start; }
         }
         if (ok) depi(G / 3 - 1);
     }
@@ -258,7 +312,7 @@ vbody(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ y, uint8_t* __
 static float bf(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
 
 int main(int argc, char** argv) {
-    const int reps = argc > 1 ? atoi(argv[1]) : 10;
+    const int reps = argc > 1 ? atoi(argv[1]) : 10, tlmode = argc > 2 ? atoi(argv[2]) : 0;
     // 12-tap windowed-sinc low-pass (cutoff 0.25 of the up-res rate), the shape of the reference's design_lowpass_filter output
     float f[12], sum = 0.f;
     for (int i = 0; i < 12; i++) { const float x = (i - 5.5f) * 0.5f, w = 0.5f - 0.5f * cosf(2.f * 3.14159265f * (i + 0.5f) / 12.f); f[i] = (fabsf(x) < 1e-6f ? 1.f : sinf(3.14159265f * x) / (3.14159265f * x)) * w; sum += f[i]; }
@@ -276,6 +330,7 @@ int main(int argc, char** argv) {
     uint8_t *d_in, *d_mask; __nv_bfloat16* d_y; int* d_err; long long* d_cyc;
     const size_t ybytes = (size_t)PLANES * OH * OW * 2, mbytes = (size_t)PLANES * UH * MASK_PITCH;
     cudaMalloc(&d_in, packed.size() * 2); cudaMalloc(&d_y, ybytes); cudaMalloc(&d_mask, mbytes); cudaMalloc(&d_err, 4); cudaMalloc(&d_cyc, 148 * 8);
+    long long* d_tl; cudaMalloc(&d_tl, 64 * 8 * 8); cudaMemset(d_tl, 0, 64 * 8 * 8);
     cudaMemcpy(d_in, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice);
     cudaFuncSetAttribute(vbody, cudaFuncAttributeMaxDynamicSharedMemorySize, OFF_END);
     printf("vbody probe: %d planes, shared memory %d bytes per CTA, 148 CTAs x %d threads\n", PLANES, OFF_END, NTHREADS);
@@ -298,7 +353,7 @@ int main(int argc, char** argv) {
     std::vector<__nv_bfloat16> hy(OH * OW); std::vector<uint8_t> hm((size_t)UH * MASK_PITCH);
     for (int swapB = 0; swapB < 2; swapB++) {
         cudaMemset(d_err, 0, 4); cudaMemset(d_y, 0xff, ybytes); cudaMemset(d_mask, 0xff, mbytes);
-        vbody<<<148, NTHREADS, OFF_END>>>(d_in, d_y, d_mask, d_err, d_cyc, swapB);
+        vbody<<<148, NTHREADS, OFF_END>>>(d_in, d_y, d_mask, d_err, d_cyc, swapB, 0, nullptr);
         cudaError_t e = cudaDeviceSynchronize();
         int herr = 0; cudaMemcpy(&herr, d_err, 4, cudaMemcpyDeviceToHost);
         printf("B descriptor %s: launch %s, timeout flag %d\n", swapB ? "lbo = column-group stride, sbo = 128" : "lbo = 128 (K groups), sbo = column-group stride", cudaGetErrorString(e), herr);
@@ -320,18 +375,34 @@ int main(int argc, char** argv) {
         printf("  => %s\n", good ? "PARITY OK (2e-2 of BASELINE.json for 16-bit I/O)" : "MISMATCH");
         if (!good) continue;
         cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
-        float best = 1e9f, tot = 0.f;
-        for (int i = 0; i < reps; i++) {
-            cudaEventRecord(e0);
-            vbody<<<148, NTHREADS, OFF_END>>>(d_in, d_y, d_mask, d_err, d_cyc, swapB);
-            cudaEventRecord(e1); cudaEventSynchronize(e1);
-            float ms = 0; cudaEventElapsedTime(&ms, e0, e1); tot += ms; if (ms < best) best = ms;
-        }
+        auto timed = [&](int mode, float& best, float& avg) {
+            best = 1e9f; float tot = 0.f;
+            for (int i = 0; i < reps; i++) {
+                cudaEventRecord(e0);
+                vbody<<<148, NTHREADS, OFF_END>>>(d_in, d_y, d_mask, d_err, d_cyc, swapB, mode, nullptr);
+                cudaEventRecord(e1); cudaEventSynchronize(e1);
+                float ms = 0; cudaEventElapsedTime(&ms, e0, e1); tot += ms; if (ms < best) best = ms;
+            }
+            avg = tot / reps;
+        };
+        float best, avg;
+        timed(0, best, avg);
+        const float tot = avg * reps;
         long long hc[148]; cudaMemcpy(hc, d_cyc, sizeof(hc), cudaMemcpyDeviceToHost);
         long long cmax = 0; for (int i = 0; i < 148; i++) if (hc[i] > cmax) cmax = hc[i];
         printf("  %d launches: average %.1f us, best %.1f us per launch of %d planes; slowest CTA %lld cycles = %.0f cycles per plane (14 planes)\n",
                reps, tot / reps * 1e3, best * 1e3, PLANES, cmax, cmax / 14.0);
         printf("  written per launch: y %.1f MB + mask %.1f MB; read (L2-resident set) %.1f MB\n", ybytes / 1e6, mbytes / 1e6, (double)PLANES * 2 * AH_BYTES / 1e6);
+        struct { int mode; const char* name; } abl[] = {{16, "A1 from tensor memory (instead of shared memory)"}, {8, "input resident (no reloads from L2)"}, {8 + 1, "resident, no MMA issued"},
+            {8 + 2, "resident, no EPI1"}, {8 + 4, "resident, no EPI2"}, {8 + 6, "resident, MMA only"}, {8 + 7, "resident, barriers only"}, {8 + 32, "resident, no mask stores"}, {8 + 64, "resident, no y stores"}, {8 + 96, "resident, no global stores at all"}, {1, "no MMA issued"}, {6, "MMA only"}, {7, "barriers and loads only"}};
+        for (auto& a : abl) { float b2, a2; timed(a.mode, b2, a2); printf("  ablation %2d  %-50s average %.1f us, best %.1f us\n", a.mode, a.name, a2 * 1e3, b2 * 1e3); }
+        vbody<<<148, NTHREADS, OFF_END>>>(d_in, d_y, d_mask, d_err, d_cyc, swapB, tlmode, d_tl);
+        cudaDeviceSynchronize();
+        long long htl[64 * 8]; cudaMemcpy(htl, d_tl, sizeof(htl), cudaMemcpyDeviceToHost);
+        printf("  timeline (mode %d) of CTA 0 (cycles since kernel start): step | mma1 issued | mma2: v_full seen, issued | epi: u_full seen, v_empty seen, epi1 done, epi2 done\n", tlmode);
+        for (int g = 0; g < 30; g++) printf("   %2d (t=%d) | %7lld | %7lld %7lld | %7lld %7lld %7lld %7lld\n", g, g % 3, htl[g * 8], htl[g * 8 + 1], htl[g * 8 + 2], htl[g * 8 + 3], htl[g * 8 + 4], htl[g * 8 + 5], htl[g * 8 + 6]);
+        int herr2 = 0; cudaMemcpy(&herr2, d_err, 4, cudaMemcpyDeviceToHost);
+        printf("  timeout flag after the ablations: %d\n", herr2);
         break;
     }
     return 0;
