@@ -156,6 +156,21 @@ int cno_film_bwd_finish(const float* s1, const float* s2, const float* t, const 
 int cno_cin_fwd_noalloc(const void* x, void* y, const float* gamma, const float* beta, const float* scale,
                         const float* shift, int dtype, int n, int c, int hw, float eps, void* stream);
 
+/* Optimiser step of the training loop (TrainCNO_time_L.py:185-196 `optimizer.step()` of the `torch.optim.AdamW` built in
+ * CNO_timeModule_CIN.py:996; CNO_FineTune.py: three parameter groups): AdamW over EVERY parameter tensor in one launch.
+ * `table` (device memory) has one record per tensor, `chunk_tensor[n_chunks]` (device) maps each chunk of cno_adamw_chunk() elements
+ * to its tensor (a tensor's chunks are consecutive, starting at first_chunk).  `step` (device, fp32[1]) is incremented first, then
+ *   p *= 1 - lr*wd;  m += (1-b1)(g-m);  v = b2 v + (1-b2) g^2;  p -= lr/(1-b1^t) * m / (sqrt(v)/sqrt(1-b2^t) + eps)
+ * (torch.optim.AdamW, amsgrad = maximize = False).  A record with grad = NULL is skipped.  fp32 only; pointers need 4-byte alignment
+ * (16-byte aligned tensors take the vector path). */
+typedef struct CnoAdamTensor {
+    float* param; const float* grad; float* exp_avg; float* exp_avg_sq;
+    int64_t numel; float lr, weight_decay; int first_chunk, pad;
+} CnoAdamTensor;
+int cno_adamw_chunk(void);
+int cno_adamw_multi(const CnoAdamTensor* table, const int* chunk_tensor, int n_chunks, float* step,
+                    double beta1, double beta2, double eps, void* stream);
+
 /* Measurement helper used by bench.py / tests (not part of the reference surface): FP32 FMA issue
  * rate probe.  variant 0 = scalar FFMA, 1 = packed fma.rn.f32x2.  Writes elapsed-cycle-independent
  * results to out[threads]; returns 0. */

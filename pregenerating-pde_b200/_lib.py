@@ -28,6 +28,8 @@ SIGNATURES = {
     'cno_filtered_lrelu_affine': (_I, [_P] * 7 + [_I] * 19 + [_F, _F, _F, _I, _P, _P, _P]),
     'cno_film_bwd_finish': (_I, [_P] * 22 + [_I] * 3 + [_P]),
     'cno_cin_fwd_noalloc': (_I, [_P] * 6 + [_I] * 4 + [_F, _P]),
+    'cno_adamw_chunk': (_I, []),
+    'cno_adamw_multi': (_I, [_P, _P, _I, _P, C.c_double, C.c_double, C.c_double, _P]),
     'cno_probe_fma': (_I, [_P, _I, _I, _I, _I, _P]),
 }
 

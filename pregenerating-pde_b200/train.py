@@ -102,7 +102,7 @@ class Trainer:
     `graph=True` the whole step (forward, backward, bucket copies + all-reduces on the forked stream, AdamW) replays as one
     CUDA graph per rank.  `mode='finetune'`: CNO_FineTune.py workload (finetune.initialize_FT wrappers, three AdamW groups)."""
 
-    def __init__(self, cfg=None, device='cuda', ddp=False, graph=False, autocast=None, buckets=4, mode='train', ft=None, side_stream=True):
+    def __init__(self, cfg=None, device='cuda', ddp=False, graph=False, autocast=None, buckets=4, mode='train', ft=None, side_stream=True, optimizer='multi'):
         self.device = torch.device(device)
         if mode == 'finetune':
             from . import finetune
@@ -148,8 +148,12 @@ class Trainer:
             wd = ft['model']['weight_decay']
         else:
             groups, wd = [{'params': self.params, 'lr': self.model.lr}], self.model.weight_decay
-        self.opt = torch.optim.AdamW(groups, lr=self.model.lr, weight_decay=wd, capturable=bool(graph and self.device.type == 'cuda'),
-                                     **(dict(fused=True) if self.device.type == 'cuda' else {}))    # one multi-tensor kernel family
+        if self.device.type == 'cuda' and optimizer == 'multi':
+            from .optim import MultiTensorAdamW          # every parameter tensor of every group in ONE launch (csrc/adamw.cu)
+            self.opt = MultiTensorAdamW(groups, lr=self.model.lr, weight_decay=wd)
+        else:                                            # optimizer='torch': torch's fused multi-tensor AdamW (~32 launches, 0.8 ms)
+            self.opt = torch.optim.AdamW(groups, lr=self.model.lr, weight_decay=wd, capturable=bool(graph and self.device.type == 'cuda'),
+                                         **(dict(fused=True) if self.device.type == 'cuda' else {}))
         # FILM parameter gradients on a side stream (cin.PARAM_GRAD_STREAM): joined before they are gathered / used by AdamW
         self._side = None
         if self.device.type == 'cuda' and side_stream:
