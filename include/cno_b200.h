@@ -171,6 +171,12 @@ int cno_adamw_chunk(void);
 int cno_adamw_multi(const CnoAdamTensor* table, const int* chunk_tensor, int n_chunks, float* step,
                     double beta1, double beta2, double eps, void* stream);
 
+/* NCHW <-> NHWC conversion of a dense [n, c, hw] / [n, hw, c] tensor around the cuDNN convolutions of the CNO blocks
+ * (CNO_timeModule_CIN.py:329-335, :495-510; the reference leaves the conversion to cuDNN, which repeats it for every operand of every
+ * pass): per sample a tiled matrix transpose.  x and y must not overlap. */
+int cno_nchw_to_nhwc(const void* x, void* y, int dtype, int n, int c, int hw, void* stream);
+int cno_nhwc_to_nchw(const void* x, void* y, int dtype, int n, int c, int hw, void* stream);
+
 /* Measurement helper used by bench.py / tests (not part of the reference surface): FP32 FMA issue
  * rate probe.  variant 0 = scalar FFMA, 1 = packed fma.rn.f32x2.  Writes elapsed-cycle-independent
  * results to out[threads]; returns 0. */

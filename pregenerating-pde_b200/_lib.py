@@ -30,6 +30,8 @@ SIGNATURES = {
     'cno_cin_fwd_noalloc': (_I, [_P] * 6 + [_I] * 4 + [_F, _P]),
     'cno_adamw_chunk': (_I, []),
     'cno_adamw_multi': (_I, [_P, _P, _I, _P, C.c_double, C.c_double, C.c_double, _P]),
+    'cno_nchw_to_nhwc': (_I, [_P, _P, _I, _I, _I, _I, _P]),
+    'cno_nhwc_to_nchw': (_I, [_P, _P, _I, _I, _I, _I, _P]),
     'cno_probe_fma': (_I, [_P, _I, _I, _I, _I, _P]),
 }
 

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 OBJ = os.path.join(os.path.dirname(HERE), 'build', 'cno_b200')
 LIB = os.path.join(HERE, 'libcno_b200.so')
-SOURCES = ['capi.cu', 'bias_act.cu', 'upfirdn2d.cu', 'flrelu_act.cu', 'cin.cu', 'adamw.cu', 'flrelu_fused.cu',
+SOURCES = ['capi.cu', 'bias_act.cu', 'upfirdn2d.cu', 'flrelu_act.cu', 'cin.cu', 'adamw.cu', 'layout.cu', 'flrelu_fused.cu',
            'flrelu_fused_f32.cu', 'flrelu_fused_bf16.cu', 'flrelu_fused_f16.cu',
            'flrelu_plane_f32.cu', 'flrelu_plane_bf16.cu', 'flrelu_plane_f16.cu'] + \
           [f'flrelu_fused_{t}_p{i}.cu' for t in ('f32', 'bf16', 'f16') for i in range(5)]

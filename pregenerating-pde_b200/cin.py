@@ -239,6 +239,7 @@ def film_forward(self, x, timestep, residual=None):
 
 
 SKIP_DEAD_BIAS = os.environ.get('CNO_KEEP_CONV_BIAS', '0') == '0'
+CONV_CHANNELS_LAST = os.environ.get('CNO_CONV_CHANNELS_LAST', '1') == '1'
 
 
 def conv_before_film(conv, film, x):
@@ -252,6 +253,13 @@ def conv_before_film(conv, film, x):
     norm = getattr(film, 'norm', None)
     if (SKIP_DEAD_BIAS and conv.bias is not None and isinstance(norm, torch.nn.InstanceNorm2d) and not norm.track_running_stats
             and isinstance(conv, torch.nn.Conv2d) and type(conv).forward is torch.nn.Conv2d.forward and conv.padding_mode == 'zeros'):
+        if CONV_CHANNELS_LAST and x.is_cuda and isinstance(conv.padding, tuple) and x.dtype in _DT and x.dtype != torch.float64:
+            # cuDNN's tensor-op convolutions are NHWC inside: fed NCHW tensors, every pass converts its operands itself - x for the
+            # forward AND again for the weight gradient, dy for the data AND again for the weight gradient, y and dx back - six
+            # activation-sized transposes per convolution and training step (7.5 ms of the step, section 6).  With the conversion made
+            # explicit (layout.py, csrc/layout.cu) the NHWC x is kept for the backward and dy is converted once: four transposes.
+            from . import layout
+            return layout.conv2d_nhwc(x, conv.weight, conv.stride, conv.padding, conv.dilation, conv.groups)
         return torch.nn.functional.conv2d(x, conv.weight, None, conv.stride, conv.padding, conv.dilation, conv.groups)
     return conv(x)
 

@@ -846,3 +846,43 @@ def test_two_devices_one_process(cno):
         up = cno.upfirdn2d.upsample2d(x.to(dev), cfg['fu'].to(dev), up=2)
         assert rel(y, y_ref) < 1e-5
         assert rel(up, O.upfirdn2d(x, cfg['fu'], up=2, padding=[6, 5, 6, 5], gain=4)) < 1e-5
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize('shape', [(2, 7, 16, 16), (3, 32, 33, 17), (1, 5, 8, 8), (2, 64, 128, 128), (1, 256, 8, 8), (2, 33, 1, 40), (0, 4, 8, 8)])
+def test_layout_transposes(cno, shape, dtype):
+    """cno_nchw_to_nhwc / cno_nhwc_to_nchw (csrc/layout.cu): bit-exact against torch's memory-format copies, ragged sizes included"""
+    from pregenerating_pde_b200 import layout
+    g = torch.Generator().manual_seed(sum(shape))
+    x = torch.randn(shape, generator=g).to(DEV, dtype)
+    y = layout.to_nhwc(x)
+    assert y.shape == x.shape and (x.numel() == 0 or y.is_contiguous(memory_format=torch.channels_last))
+    assert torch.equal(y, x)
+    assert torch.equal(y.permute(0, 2, 3, 1).contiguous(), x.permute(0, 2, 3, 1).contiguous())      # the bytes, not only the logical view
+    z = layout.to_nchw(y)
+    assert z.is_contiguous() and torch.equal(z, x)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('n,cin_,cout,s,k', [(2, 7, 16, 32, 3), (3, 32, 32, 16, 3), (2, 64, 128, 8, 3), (1, 16, 8, 24, 1)])
+def test_conv2d_nhwc_matches_conv2d(cno, n, cin_, cout, s, k):
+    """layout.conv2d_nhwc = torch.nn.functional.conv2d (same cuDNN kernels, conversions made explicit): forward, dx and dw"""
+    from pregenerating_pde_b200 import layout
+    g = torch.Generator().manual_seed(n + cin_ + cout)
+    x = torch.randn(n, cin_, s, s, generator=g).to(DEV)
+    w = (torch.randn(cout, cin_, k, k, generator=g) * 0.1).to(DEV)
+    dy = torch.randn(n, cout, s, s, generator=g).to(DEV)
+    tf32 = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        xa, wa = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+        ya = layout.conv2d_nhwc(xa, wa, (1, 1), (k // 2, k // 2), (1, 1), 1)
+        dxa, dwa = torch.autograd.grad(ya, [xa, wa], dy)
+        xb, wb = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+        yb = torch.nn.functional.conv2d(xb, wb, None, 1, k // 2)
+        dxb, dwb = torch.autograd.grad(yb, [xb, wb], dy)
+    finally:
+        torch.backends.cudnn.allow_tf32 = tf32
+    assert ya.is_contiguous() and dxa.is_contiguous() and dwa.is_contiguous()
+    assert rel(ya, yb) < 1e-5 and rel(dxa, dxb) < 1e-5 and rel(dwa, dwb) < 1e-5
