@@ -35,31 +35,33 @@ def to_nchw(x):
 
 class _Conv2dNHWC(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, stride, padding, dilation, groups):
+    def forward(ctx, x, weight, bias, stride, padding, dilation, groups):
         x_cl = to_nhwc(x)
-        y_cl = torch.nn.functional.conv2d(x_cl, weight, None, stride, padding, dilation, groups)
-        ctx.save_for_backward(x_cl, weight)
-        ctx.cfg = (stride, padding, dilation, groups)
+        w_cl = weight.contiguous(memory_format=torch.channels_last)          # once per step; forward, data and weight gradient all use it
+        y_cl = torch.nn.functional.conv2d(x_cl, w_cl, bias, stride, padding, dilation, groups)
+        ctx.save_for_backward(x_cl, w_cl)
+        ctx.cfg = (stride, padding, dilation, groups, None if bias is None else list(bias.shape))
         return to_nchw(y_cl)
 
     @staticmethod
     def backward(ctx, dy):
-        x_cl, weight = ctx.saved_tensors
-        stride, padding, dilation, groups = ctx.cfg
+        x_cl, w_cl = ctx.saved_tensors
+        stride, padding, dilation, groups, bias_sizes = ctx.cfg
         dy_cl = to_nhwc(dy)
-        mask = [ctx.needs_input_grad[0], ctx.needs_input_grad[1], False]
-        dx_cl, dw, _ = torch.ops.aten.convolution_backward(dy_cl, x_cl, weight, None, list(stride), list(padding), list(dilation), False, [0, 0],
-                                                           groups, mask)
+        mask = [ctx.needs_input_grad[0], ctx.needs_input_grad[1], bias_sizes is not None and ctx.needs_input_grad[2]]
+        dx_cl, dw, db = torch.ops.aten.convolution_backward(dy_cl, x_cl, w_cl, bias_sizes, list(stride), list(padding), list(dilation), False, [0, 0],
+                                                            groups, mask)
         dx = to_nchw(dx_cl) if dx_cl is not None else None
         if dw is not None and not dw.is_contiguous():
             dw = dw.contiguous()
-        return dx, dw, None, None, None, None
+        return dx, dw, db, None, None, None, None
 
 
-def conv2d_nhwc(x, weight, stride=(1, 1), padding=(0, 0), dilation=(1, 1), groups=1):
-    """conv2d(x, weight) without bias on NCHW tensors, with the layout conversions cuDNN needs done once each (see module docstring).
+def conv2d_nhwc(x, weight, stride=(1, 1), padding=(0, 0), dilation=(1, 1), groups=1, bias=None):
+    """conv2d(x, weight, bias) on NCHW tensors, with the layout conversions cuDNN needs done once each (see module docstring).
     Autocast: runs in the autocast dtype like torch.nn.functional.conv2d would."""
     if torch.is_autocast_enabled('cuda'):
         dt = torch.get_autocast_dtype('cuda')
         x, weight = x.to(dt), weight.to(dt)
-    return _Conv2dNHWC.apply(x, weight, tuple(stride), tuple(padding), tuple(dilation), groups)
+        bias = None if bias is None else bias.to(dt)
+    return _Conv2dNHWC.apply(x, weight, bias, tuple(stride), tuple(padding), tuple(dilation), groups)

@@ -29,18 +29,25 @@ def test_graph_step_equals_eager_step(cno):
     the training trajectory through its losses."""
     torch.manual_seed(0)
     cfg0 = dict(SMALL, lr=0.0, weight_decay=0.0)
-    a = cno.train.Trainer(cfg0, device=DEV, graph=False)
-    b = cno.train.Trainer(cfg0, device=DEV, graph=True)
-    b.model.load_state_dict(a.model.state_dict())
     batches = [cno.train.synthetic_fpo_batch(4, size=32, device=DEV, seed=s) for s in range(3)]
-    for bt in batches + batches:
-        la, ga = float(a.step(*bt)), a.grad_vector()
-        lb, gb = float(b.step(*bt)), b.grad_vector()
-        assert torch.isfinite(gb).all()
-        assert abs(la - lb) <= 1e-5 * abs(la), (la, lb)
-        # fp32 floor: the db atomics and cuDNN's algorithm choice may differ between the warm-up and the captured launches
-        assert float((ga - gb).abs().max() / ga.abs().max()) < 1e-4
-    b.close()
+    # TF32 off for the gradient comparison: with TF32 convolutions cuDNN's algorithm choice (which may differ between the eager and the
+    # captured launches) moves gradients by ~1e-4 of their maximum, i.e. the comparison would sit on its own tolerance
+    tf32 = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        a = cno.train.Trainer(cfg0, device=DEV, graph=False)
+        b = cno.train.Trainer(cfg0, device=DEV, graph=True)
+        b.model.load_state_dict(a.model.state_dict())
+        for bt in batches + batches:
+            la, ga = float(a.step(*bt)), a.grad_vector()
+            lb, gb = float(b.step(*bt)), b.grad_vector()
+            assert torch.isfinite(gb).all()
+            assert abs(la - lb) <= 1e-5 * abs(la), (la, lb)
+            # fp32 floor: the db atomics and cuDNN's algorithm choice may differ between the warm-up and the captured launches
+            assert float((ga - gb).abs().max() / ga.abs().max()) < 1e-4
+        b.close()
+    finally:
+        torch.backends.cudnn.allow_tf32 = tf32
     # with the optimiser running: same loss trajectory (3 warm-up steps precede the capture, give the eager trainer the same history)
     torch.manual_seed(0)
     a = cno.train.Trainer(SMALL, device=DEV, graph=False)
