@@ -264,6 +264,16 @@ def conv_before_film(conv, film, x):
     return conv(x)
 
 
+def conv_nhwc(conv, x):
+    """conv(x) for a plain nn.Conv2d that keeps its bias (LiftProjectBlock's output convolution, CNO_timeModule_CIN.py:163-166): on
+    CUDA through layout.conv2d_nhwc, i.e. with the layout conversions cuDNN needs done once each instead of per pass."""
+    if (CONV_CHANNELS_LAST and x.is_cuda and isinstance(conv, torch.nn.Conv2d) and type(conv).forward is torch.nn.Conv2d.forward
+            and conv.padding_mode == 'zeros' and isinstance(conv.padding, tuple) and x.ndim == 4 and x.dtype in _DT and x.dtype != torch.float64):
+        from . import layout
+        return layout.conv2d_nhwc(x, conv.weight, conv.stride, conv.padding, conv.dilation, conv.groups, bias=conv.bias)
+    return conv(x)
+
+
 def _film_kernel_ok(self, x, timestep):
     norm = self.norm
     return (x.is_cuda and x.ndim == 4 and isinstance(norm, torch.nn.InstanceNorm2d) and norm.affine

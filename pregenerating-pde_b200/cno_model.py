@@ -163,7 +163,7 @@ class LiftProjectBlock(nn.Module):
         self.convolution = nn.Conv2d(latent_dim, out_channels, conv_kernel, stride=1, padding=(conv_kernel - 1) // 2)
 
     def forward(self, x, time):
-        return self.convolution(self.inter_CNOBlock(x, time))
+        return _cin.conv_nhwc(self.convolution, self.inter_CNOBlock(x, time))
 
 
 class ResidualBlock(nn.Module):

@@ -2,11 +2,15 @@
 they are handed NCHW tensors every pass converts its own operands: x for the forward and again for the weight gradient, dy for the
 data gradient and again for the weight gradient, y and dx back - six activation-sized transposes per convolution and training step.
 `conv2d_nhwc` converts x once (and keeps the NHWC copy for the backward), dy once, and y / dx back: four, on our own tiled kernel."""
+import contextlib
+import os
+
 import torch
 
 from . import _lib
 from .torch_utils.custom_ops import _ptr, _stream
 
+WGRAD_SIDE_STREAM = os.environ.get('CNO_WGRAD_SIDE_STREAM', '1') == '1'
 _DT = {torch.float32: _lib.F32, torch.bfloat16: _lib.BF16, torch.float16: _lib.F16}
 
 
@@ -35,8 +39,11 @@ def to_nchw(x):
 
 class _Conv2dNHWC(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, padding, dilation, groups):
+    def forward(ctx, x, weight, bias, stride, padding, dilation, groups, cast):
         x_cl = to_nhwc(x)
+        ctx.param_dtypes = (weight.dtype, None if bias is None else bias.dtype)
+        if cast is not None:                             # autocast: parameters are cast HERE so that their gradients are cast back on the side stream
+            weight, bias = weight.to(cast), (None if bias is None else bias.to(cast))
         w_cl = weight.contiguous(memory_format=torch.channels_last)          # once per step; forward, data and weight gradient all use it
         y_cl = torch.nn.functional.conv2d(x_cl, w_cl, bias, stride, padding, dilation, groups)
         ctx.save_for_backward(x_cl, w_cl)
@@ -48,13 +55,30 @@ class _Conv2dNHWC(torch.autograd.Function):
         x_cl, w_cl = ctx.saved_tensors
         stride, padding, dilation, groups, bias_sizes = ctx.cfg
         dy_cl = to_nhwc(dy)
-        mask = [ctx.needs_input_grad[0], ctx.needs_input_grad[1], bias_sizes is not None and ctx.needs_input_grad[2]]
-        dx_cl, dw, db = torch.ops.aten.convolution_backward(dy_cl, x_cl, w_cl, bias_sizes, list(stride), list(padding), list(dilation), False, [0, 0],
-                                                            groups, mask)
-        dx = to_nchw(dx_cl) if dx_cl is not None else None
-        if dw is not None and not dw.is_contiguous():
-            dw = dw.contiguous()
-        return dx, dw, db, None, None, None, None
+        args = (list(stride), list(padding), list(dilation), False, [0, 0], groups)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:                      # the data gradient is what the rest of backward waits for
+            dx_cl = torch.ops.aten.convolution_backward(dy_cl, x_cl, w_cl, bias_sizes, *args, [True, False, False])[0]
+            dx = to_nchw(dx_cl)
+        want_b = bias_sizes is not None and ctx.needs_input_grad[2]
+        if ctx.needs_input_grad[1] or want_b:
+            # the weight gradient (a quarter of the training step in cuDNN's wgrad kernels) is needed only by the optimiser: it runs on
+            # the parameter-gradient side stream (cin.PARAM_GRAD_STREAM, set by the Trainer and joined before gradients are used),
+            # under the activation / CIN kernels of the layers below
+            from . import cin as _cin
+            side = _cin.PARAM_GRAD_STREAM if (_cin.PARAM_GRAD_STREAM is not None and _cin.PARAM_GRAD_STREAM.device == dy.device and WGRAD_SIDE_STREAM) else None
+            if side is not None:
+                side.wait_stream(torch.cuda.current_stream(dy.device))
+                _cin._side_keepalive.append((dy_cl, x_cl, w_cl))
+            with (torch.cuda.stream(side) if side is not None else contextlib.nullcontext()):
+                _, dw, db = torch.ops.aten.convolution_backward(dy_cl, x_cl, w_cl, bias_sizes, *args, [False, ctx.needs_input_grad[1], want_b])
+                if dw is not None:
+                    dw = dw.to(ctx.param_dtypes[0]).contiguous()
+                if db is not None:
+                    db = db.to(ctx.param_dtypes[1])
+                # dw / db are NOT put on the keep-alive list: autograd must be able to adopt them as .grad without a copy (a second
+                # reference would make AccumulateGrad clone them on the main stream, before the side stream has written them)
+        return dx, dw, db, None, None, None, None, None
 
 
 def conv2d_nhwc(x, weight, stride=(1, 1), padding=(0, 0), dilation=(1, 1), groups=1, bias=None):
@@ -62,6 +86,5 @@ def conv2d_nhwc(x, weight, stride=(1, 1), padding=(0, 0), dilation=(1, 1), group
     Autocast: runs in the autocast dtype like torch.nn.functional.conv2d would."""
     if torch.is_autocast_enabled('cuda'):
         dt = torch.get_autocast_dtype('cuda')
-        x, weight = x.to(dt), weight.to(dt)
-        bias = None if bias is None else bias.to(dt)
-    return _Conv2dNHWC.apply(x, weight, bias, tuple(stride), tuple(padding), tuple(dilation), groups)
+        return _Conv2dNHWC.apply(x.to(dt), weight, bias, tuple(stride), tuple(padding), tuple(dilation), groups, dt)
+    return _Conv2dNHWC.apply(x, weight, bias, tuple(stride), tuple(padding), tuple(dilation), groups, None)
