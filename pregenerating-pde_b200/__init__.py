@@ -9,6 +9,7 @@ from . import _lib                                   # noqa: F401
 from .torch_utils import custom_ops                  # noqa: F401
 from .torch_utils.ops import bias_act, upfirdn2d, filtered_lrelu   # noqa: F401
 from . import cin                                    # noqa: F401
+from . import layout, optim                          # noqa: F401
 from . import cno_model, train, finetune             # noqa: F401
 from .patch import patch_reference, unpatch_reference              # noqa: F401
 
