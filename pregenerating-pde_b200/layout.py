@@ -6,6 +6,7 @@ import contextlib
 import os
 
 import torch
+from torch.autograd.function import once_differentiable
 
 from . import _lib
 from .torch_utils.custom_ops import _ptr, _stream
@@ -51,6 +52,7 @@ class _Conv2dNHWC(torch.autograd.Function):
         return to_nchw(y_cl)
 
     @staticmethod
+    @once_differentiable                                 # first-order only (the training loops need no more); a second backward raises
     def backward(ctx, dy):
         x_cl, w_cl = ctx.saved_tensors
         stride, padding, dilation, groups, bias_sizes = ctx.cfg
@@ -83,7 +85,9 @@ class _Conv2dNHWC(torch.autograd.Function):
 
 def conv2d_nhwc(x, weight, stride=(1, 1), padding=(0, 0), dilation=(1, 1), groups=1, bias=None):
     """conv2d(x, weight, bias) on NCHW tensors, with the layout conversions cuDNN needs done once each (see module docstring).
-    Autocast: runs in the autocast dtype like torch.nn.functional.conv2d would."""
+    Autocast: runs in the autocast dtype like torch.nn.functional.conv2d would.  First-order gradients only.  When
+    `cin.PARAM_GRAD_STREAM` is set (the Trainer does), weight / bias gradients are produced on that stream: whoever set it calls
+    `cin.join_param_grad_stream()` before reading them (Trainer: before the gradient all-reduce and before AdamW)."""
     if torch.is_autocast_enabled('cuda'):
         dt = torch.get_autocast_dtype('cuda')
         return _Conv2dNHWC.apply(x.to(dt), weight, bias, tuple(stride), tuple(padding), tuple(dilation), groups, dt)
