@@ -33,7 +33,7 @@ constexpr int V_BYTES = NG * 128 * 16;             // 36,864
 constexpr int A1_BYTES = 10 * 128 * 16, A2_BYTES = 8 * 256 * 16;
 constexpr int MASK_PITCH = 68;                     // bytes per mask row (272 columns / 4)
 constexpr int OFF_A1 = 0, OFF_A2 = OFF_A1 + A1_BYTES, OFF_AH = OFF_A2 + A2_BYTES, OFF_V = OFF_AH + 2 * AH_BYTES, OFF_END = OFF_V + 2 * V_BYTES;
-constexpr int NTHREADS = 352;
+constexpr int NTHREADS = 608;                     // 2 epilogue groups x 8 warps + MMA1 issuer + loader + MMA2 issuer
 constexpr float SLOPE = 0.2f;
 
 __constant__ float c_wup[2][6];                    // vertical up-FIR taps per phase (gain folded in)
@@ -152,7 +152,7 @@ vbody(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ y, uint8_t* __
     const uint32_t tU = tmem_base, tD = tmem_base + 2 * NH;                 // U0 | U1 | D, 144 columns each
     const uint32_t sA1 = smem_u32(smem + OFF_A1), sA2 = smem_u32(smem + OFF_A2), sAH = smem_u32(smem + OFF_AH), sV = smem_u32(smem + OFF_V);
 
-    if (warp == 8 || warp == 10) {
+    if (warp == 16 || warp == 18) {
         if (lane == 0) {
             // D = F32, A = B = BF16, A K-major, B MN-major (bit 16), N = 144, M = 128
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 16) | ((uint32_t)(NH >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
@@ -192,10 +192,10 @@ vbody(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ y, uint8_t* __
             // two issuing threads (measured: commit + wait + fence cost one thread ~ 450 cycles per group, ~ 1,000 per step when one thread
             // issues both groups): warp 8 issues MMA1 (as far ahead as U allows: U[g & 1] is free once EPI1(g - 2) has LOADED it),
             // warp 10 issues MMA2(g) when EPI1(g) has stored V
-            if (warp == 8) { bool ok = true; for (int g = 0; g < G && ok; g++) ok = mma1(g); }
+            if (warp == 16) { bool ok = true; for (int g = 0; g < G && ok; g++) ok = mma1(g); }
             else { bool ok = true; for (int g = 0; g < G && ok; g++) ok = mma2(g); }
         }
-    } else if (warp == 9) {
+    } else if (warp == 17) {
         if (lane == 0) {
             for (int i = 0; i < ((mode & 8) ? 2 : nplanes * 2); i++) {
                 const int pl = i >> 1, h = i & 1, plane = (int)blockIdx.x + pl * (int)gridDim.x;
@@ -208,7 +208,9 @@ vbody(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ y, uint8_t* __
             }
         }
     } else {
-        const int q = warp & 3, cg = warp >> 2;
+        // two epilogue groups of 8 warps: group 0 owns the even steps (U[0], V[0]), group 1 the odd ones - while one group sits in the
+        // ~1,000-cycle barrier chain of its next step the other one computes
+        const int grp = warp >> 3, q = warp & 3, cg = (warp >> 2) & 1;
         const uint32_t lane_off = (uint32_t)(32 * q) << 16;
         float fd[12];
 #pragma unroll
@@ -220,15 +222,17 @@ vbody(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ y, uint8_t* __
             FENCE_AFTER();
             const int oc0 = 4 * cg;
             if (!(mode & 4)) {
-                uint32_t d[5][16];                                     // column chunks oc0 .. oc0 + 4: one wait for all five loads
-#pragma unroll
-                for (int k = 0; k < 5; k++) LD16(d[k], tD + lane_off + 16 * (oc0 + k));
-                TMEM_WAIT_LD();
-                FENCE_BEFORE();
-                __syncwarp();
-                if (lane == 0) bar_arrive(&bars.d_empty);              // D is free again: the next half's MMA2 may start under the FIR below
+                uint32_t cur[16], nxt[16];                             // sliding window over the column chunks oc0 .. oc0 + 4
+                LD16(cur, tD + lane_off + 16 * oc0);
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
+                    LD16(nxt, tD + lane_off + 16 * (oc0 + k + 1));
+                    TMEM_WAIT_LD();
+                    if (k == 3) {                                      // D is in registers: the next half's MMA2 may start under the last FIR block
+                        FENCE_BEFORE();
+                        __syncwarp();
+                        if (lane == 0) bar_arrive(&bars.d_empty);
+                    }
                     uint32_t pk[4];
 #pragma unroll
                     for (int i = 0; i < 8; i += 2) {
@@ -236,13 +240,15 @@ vbody(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ y, uint8_t* __
 #pragma unroll
                         for (int tt = 0; tt < 12; tt++) {
                             const int j0 = 2 * i + tt, j1 = 2 * i + 2 + tt;
-                            a0 = fmaf(fd[tt], __uint_as_float(j0 < 16 ? d[k][j0] : d[k + 1][j0 - 16]), a0);
-                            a1 = fmaf(fd[tt], __uint_as_float(j1 < 16 ? d[k][j1] : d[k + 1][j1 - 16]), a1);
+                            a0 = fmaf(fd[tt], __uint_as_float(j0 < 16 ? cur[j0] : nxt[j0 - 16]), a0);
+                            a1 = fmaf(fd[tt], __uint_as_float(j1 < 16 ? cur[j1] : nxt[j1 - 16]), a1);
                         }
                         __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
                         pk[i >> 1] = *reinterpret_cast<uint32_t*>(&hh);
                     }
                     if (!(mode & 64) || pk[0] == 0x12345678u) *reinterpret_cast<uint4*>(y + ((size_t)plane * OH + o) * OW + 64 * h + 8 * (oc0 + k)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+#pragma unroll
+                    for (int i = 0; i < 16; i++) cur[i] = nxt[i];
                 }
                 return true;
             }
@@ -252,56 +258,62 @@ vbody(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ y, uint8_t* __
             return true;
         };
         bool ok = true;
-        for (int g = 0; g < G && ok; g++) {
+        for (int g = grp; g < G && ok; g += 2) {
             const int t = g % 3, hc = g / 3, h = hc & 1, pl = hc >> 1, b = g & 1, plane = (int)blockIdx.x + pl * (int)gridDim.x;
             if (!warp_wait(&bars.u_full[b], (g >> 1) & 1, abort, lane)) { ok = false; break; }
             if (tl && blockIdx.x == 0 && g < 64 && tid == 0) tl[g * 8 + 3] = clock64() - t_start;
             FENCE_AFTER();
             const bool active = (t < 2 || q == 0) && !(mode & 2);
             const int ch0 = cg ? 5 : 0, nch = cg ? 4 : 5;
-            uint32_t rr[5][16];
-            if (active) {
+            // TMEM loads in batches of 2 + 2 + 1 chunks of 16 columns (608 threads leave 104 registers each), each batch processed under the next
+            // one's loads; U is released after the last wait
+            uint32_t ra[2][16], rb[2][16];
+            const int krow = 32 * q + lane, r = 128 * t + krow;
+            uint8_t* vdst = smem + OFF_V + b * V_BYTES + krow * 16;
+            uint8_t* mrow = mask + ((size_t)plane * UH + (r < UH ? r : 0)) * MASK_PITCH + 32 * h;
+            auto chunk = [&](const uint32_t* rr, int ch) {
+                uint32_t pk[8], bq[4] = {0, 0, 0, 0};                                          // four independent chains, one per mask byte
 #pragma unroll
-                for (int k = 0; k < 5; k++) if (k < nch) LD16(rr[k], tU + b * NH + lane_off + 16 * (ch0 + k));
+                for (int i = 3; i >= 0; i--)
+#pragma unroll
+                    for (int j = 0; j < 4; j++) bq[j] = __funnelshift_l(rr[4 * j + i], bq[j], 2);       // (b << 2) | top two bits of the value
+                const uint32_t bits = __byte_perm(__byte_perm(bq[0], bq[1], 0x0040), __byte_perm(bq[2], bq[3], 0x0040), 0x5410);
+#pragma unroll
+                for (int i = 0; i < 16; i += 2) {
+                    float a = __uint_as_float(rr[i]), c = __uint_as_float(rr[i + 1]);
+                    a = fmaxf(a, SLOPE * a); c = fmaxf(c, SLOPE * c);
+                    __nv_bfloat162 hh = __floats2bfloat162_rn(a, c);
+                    pk[i >> 1] = *reinterpret_cast<uint32_t*>(&hh);
+                }
+                *reinterpret_cast<uint4*>(vdst + (2 * ch) * 2048) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                *reinterpret_cast<uint4*>(vdst + (2 * ch + 1) * 2048) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                if (r < UH && !(h == 1 && ch == 0) && !(mode & 32)) *reinterpret_cast<uint32_t*>(mrow + 4 * ch) = (bits >> 1) & 0x55555555u;   // code 1 = negative
+            };
+            if (active) {
+                LD16(ra[0], tU + b * NH + lane_off + 16 * ch0); LD16(ra[1], tU + b * NH + lane_off + 16 * (ch0 + 1));
+                TMEM_WAIT_LD();
+                LD16(rb[0], tU + b * NH + lane_off + 16 * (ch0 + 2)); LD16(rb[1], tU + b * NH + lane_off + 16 * (ch0 + 3));
+            }
+            if (!warp_wait(&bars.v_empty[b], ((g >> 1) & 1) ^ 1, abort, lane)) { ok = false; break; }
+            if (tl && blockIdx.x == 0 && g < 64 && tid == 0) tl[g * 8 + 4] = clock64() - t_start;
+            if (active) {
+                chunk(ra[0], ch0); chunk(ra[1], ch0 + 1);                                  // under the second batch of loads
+                TMEM_WAIT_LD();
+                if (nch == 5) LD16(ra[0], tU + b * NH + lane_off + 16 * (ch0 + 4));
+                chunk(rb[0], ch0 + 2); chunk(rb[1], ch0 + 3);
                 TMEM_WAIT_LD();
             }
             FENCE_BEFORE();
             __syncwarp();
             if (lane == 0) bar_arrive(&bars.u_empty[b]);              // U[b] is in registers: MMA1 of step g + 2 may overwrite it
-            if (!warp_wait(&bars.v_empty[b], ((g >> 1) & 1) ^ 1, abort, lane)) { ok = false; break; }
-            if (tl && blockIdx.x == 0 && g < 64 && tid == 0) tl[g * 8 + 4] = clock64() - t_start;
-            if (active) {
-                const int krow = 32 * q + lane, r = 128 * t + krow;
-                uint8_t* vdst = smem + OFF_V + b * V_BYTES + krow * 16;
-                uint8_t* mrow = mask + ((size_t)plane * UH + (r < UH ? r : 0)) * MASK_PITCH + 32 * h;
-#pragma unroll
-                for (int k = 0; k < 5; k++) if (k < nch) {
-                    const int ch = ch0 + k;
-                    uint32_t pk[8], bq[4] = {0, 0, 0, 0};                                          // four independent chains, one per mask byte
-#pragma unroll
-                    for (int i = 3; i >= 0; i--)
-#pragma unroll
-                        for (int j = 0; j < 4; j++) bq[j] = __funnelshift_l(rr[k][4 * j + i], bq[j], 2);   // (b << 2) | top two bits of the value
-                    const uint32_t bits = __byte_perm(__byte_perm(bq[0], bq[1], 0x0040), __byte_perm(bq[2], bq[3], 0x0040), 0x5410);
-#pragma unroll
-                    for (int i = 0; i < 16; i += 2) {
-                        float a = __uint_as_float(rr[k][i]), c = __uint_as_float(rr[k][i + 1]);
-                        a = fmaxf(a, SLOPE * a); c = fmaxf(c, SLOPE * c);
-                        __nv_bfloat162 hh = __floats2bfloat162_rn(a, c);
-                        pk[i >> 1] = *reinterpret_cast<uint32_t*>(&hh);
-                    }
-                    *reinterpret_cast<uint4*>(vdst + (2 * ch) * 2048) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                    *reinterpret_cast<uint4*>(vdst + (2 * ch + 1) * 2048) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-                    if (r < UH && !(h == 1 && ch == 0) && !(mode & 32)) *reinterpret_cast<uint32_t*>(mrow + 4 * ch) = (bits >> 1) & 0x55555555u;   // code 1 = negative
-                }
-            }
+            if (active && nch == 5) chunk(ra[0], ch0 + 4);
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
             if (lane == 0) bar_arrive(&bars.v_full[b]);
             if (tl && blockIdx.x == 0 && g < 64 && tid == 0) tl[g * 8 + 5] = clock64() - t_start;
             if (t == 0 && g > 0) { ok = depi(hc - 1); if (tl && blockIdx.x == 0 && g < 64 && tid == 0) tl[g * 8 + 6] = clock64() - t_start; }
         }
-        if (ok) depi(G / 3 - 1);
+        if (ok && grp == 1) depi(G / 3 - 1);            // G is even: the last step belongs to group 1
     }
     FENCE_BEFORE();
     __syncthreads();
