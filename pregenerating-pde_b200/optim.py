@@ -17,6 +17,16 @@ _RECORD = np.dtype([('param', '<u8'), ('grad', '<u8'), ('exp_avg', '<u8'), ('exp
 assert _RECORD.itemsize == 56
 
 
+def _dense(t):
+    """every element of the storage range exactly once (contiguous in some dimension order)"""
+    return t.is_contiguous() or (t.ndim == 4 and t.is_contiguous(memory_format=torch.channels_last)) or t.is_non_overlapping_and_dense()
+
+
+def _same_layout(a, b):
+    """same strides on every dimension that has more than one element"""
+    return a.shape == b.shape and all(sa == sb for n, sa, sb in zip(a.shape, a.stride(), b.stride()) if n > 1)
+
+
 class MultiTensorAdamW(torch.optim.Optimizer):
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2):
         if not (0.0 <= betas[0] < 1.0 and 0.0 <= betas[1] < 1.0):
@@ -30,8 +40,8 @@ class MultiTensorAdamW(torch.optim.Optimizer):
             if tuple(g['betas']) != tuple(betas) or g['eps'] != eps:
                 raise ValueError('one (betas, eps) pair for all groups')          # one launch, one set of scalars
             for p in g['params']:
-                if p.dtype != torch.float32 or p.device != dev or not p.is_contiguous() or dev.type != 'cuda':
-                    raise ValueError('MultiTensorAdamW: contiguous fp32 CUDA parameters on one device')
+                if p.dtype != torch.float32 or p.device != dev or not _dense(p) or dev.type != 'cuda':
+                    raise ValueError('MultiTensorAdamW: dense fp32 CUDA parameters on one device')
         self._lib = _lib.load()                                                  # raises without the CUDA library: no fallback
         self._chunk = int(self._lib.cno_adamw_chunk())
         total = sum(p.numel() for p in self._params)
@@ -42,7 +52,9 @@ class MultiTensorAdamW(torch.optim.Optimizer):
         self._first_chunk = []
         for i, p in enumerate(self._params):
             n = p.numel()
-            self.state[p] = dict(step=self._step, exp_avg=self._m[o:o + n].view_as(p), exp_avg_sq=self._v[o:o + n].view_as(p))
+            # the update is elementwise over storage: moments (and gradients) must share the parameter's strides (e.g. channels_last weights)
+            self.state[p] = dict(step=self._step, exp_avg=self._m[o:o + n].as_strided(p.shape, p.stride()),
+                                 exp_avg_sq=self._v[o:o + n].as_strided(p.shape, p.stride()))
             nch = (n + self._chunk - 1) // self._chunk
             self._first_chunk.append(first)
             chunk_tensor += [i] * nch
@@ -65,8 +77,8 @@ class MultiTensorAdamW(torch.optim.Optimizer):
         for g in self.param_groups:
             for p in g['params']:
                 gr = p.grad
-                if gr is not None and (gr.dtype != torch.float32 or not gr.is_contiguous() or gr.is_sparse):
-                    raise RuntimeError('MultiTensorAdamW: dense contiguous fp32 gradients')
+                if gr is not None and (gr.dtype != torch.float32 or gr.is_sparse or not _same_layout(gr, p)):
+                    raise RuntimeError('MultiTensorAdamW: dense fp32 gradients with the strides of their parameter')
                 st = self.state[p]
                 rec[i] = (p.data_ptr(), 0 if gr is None else gr.data_ptr(), st['exp_avg'].data_ptr(), st['exp_avg_sq'].data_ptr(), p.numel(),
                           float(g['lr']), float(g['weight_decay']), self._first_chunk[i], 0)

@@ -128,7 +128,7 @@ class Trainer:
             nb = max(1, min(int(buckets), len(order)))
             target, o, start, members = total / nb, 0, 0, []
             for p in order:
-                self._views[p] = self.flat_grad[o:o + p.numel()].view_as(p)
+                self._views[p] = self.flat_grad[o:o + p.numel()].as_strided(p.shape, p.stride())     # same layout as the parameter
                 self._bucket_of[p] = len(self.buckets)
                 members.append(p)
                 o += p.numel()

@@ -113,3 +113,31 @@ def test_rejects_unsupported(cno):
         MultiTensorAdamW([torch.nn.Parameter(torch.zeros(4, device=DEV, dtype=torch.bfloat16))])
     lib = cno._lib.load()
     assert lib.cno_adamw_multi(None, None, 0, None, 0.9, 0.999, 1e-8, None) != 0
+
+
+def test_channels_last_parameters(cno):
+    """parameters stored channels_last (the Trainer's convolution weights): moments share their strides, the update is elementwise over
+    storage and equals torch.optim.AdamW on the same tensors"""
+    from pregenerating_pde_b200.optim import MultiTensorAdamW
+    g = torch.Generator().manual_seed(3)
+    shapes = [(16, 8, 3, 3), (8, 1, 3, 3), (4, 16, 1, 1), (5,)]
+    mk = lambda: [torch.nn.Parameter(torch.randn(s, generator=torch.Generator().manual_seed(i)).to(DEV)) for i, s in enumerate(shapes)]
+    pa, pb = mk(), mk()
+    for p in pa:
+        if p.ndim == 4:
+            p.data = p.data.contiguous(memory_format=torch.channels_last)
+    oa, ob = MultiTensorAdamW(pa, lr=1e-2), torch.optim.AdamW(pb, lr=1e-2)
+    for _ in range(4):
+        for a, b in zip(pa, pb):
+            gr = torch.randn(a.shape, generator=g).to(DEV)
+            a.grad = gr.contiguous(memory_format=torch.channels_last) if a.ndim == 4 else gr.clone()
+            b.grad = gr.clone()
+        oa.step(); ob.step()
+    for a, b in zip(pa, pb):
+        assert rel(a.detach(), b.detach()) < 2e-6
+        assert rel(oa.state[a]['exp_avg'], ob.state[b]['exp_avg']) < 1e-5
+    bad = torch.nn.Parameter(torch.randn(16, 8, 3, 3, device=DEV).contiguous(memory_format=torch.channels_last))
+    ob2 = MultiTensorAdamW([bad], lr=1e-3)
+    bad.grad = torch.randn(16, 8, 3, 3, device=DEV)            # NCHW gradient for a channels_last parameter: refused, not silently permuted
+    with pytest.raises(RuntimeError):
+        ob2.step()
