@@ -367,12 +367,16 @@ def test_upfirdn2d_helpers_and_identity(cno):
 def test_upfirdn2d_full_size_adjoint(cno, shape, f_taps, kw):
     """sweep-size planes: <y, dy> == <x, dx> (the backward is the adjoint op, upfirdn2d.py:248-258)."""
     f = O.design_lowpass_filter(f_taps, 64 / 2.0001, 2 * (0.8 * 64 - 64 / 2.0001), 256).to(DEV)
-    x = torch.randn(*shape, device=DEV).requires_grad_(True)
+    gen = torch.Generator(device=DEV).manual_seed(17)
+    x = torch.randn(*shape, device=DEV, generator=gen).requires_grad_(True)
     y = cno.upfirdn2d.upfirdn2d(x, f, **kw)
-    dy = torch.randn_like(y)
+    dy = torch.randn(y.shape, device=DEV, generator=gen)
     dx, = torch.autograd.grad(y, [x], dy)
     lhs, rhs = (y.double() * dy.double()).sum(), (x.double() * dx.double()).sum()
-    assert abs(float(lhs - rhs)) / abs(float(lhs)) < 1e-5
+    # the two inner products are sums of 3e7 signed terms and can cancel to almost nothing (an unseeded run once drew lhs = 0.6 against a
+    # term scale of 3e7): the error is measured against the sum of the terms' magnitudes, not against the cancelled sum
+    scale = (y.double() * dy.double()).abs().sum()
+    assert abs(float(lhs - rhs)) / float(scale) < 1e-6
     ref = O.upfirdn2d(x.detach()[:1, :2].cpu(), f.cpu(), **kw)
     assert rel(y[:1, :2], ref) < 1e-5
 
@@ -420,6 +424,7 @@ def test_bias_act_golden(cno, golden, act):
 
 @pytest.mark.parametrize('act', ['tanh', 'sigmoid', 'elu', 'selu', 'softplus', 'swish', 'lrelu'])
 def test_bias_act_second_order_fp64(cno, act):
+    torch.manual_seed(len(act))
     x = torch.randn(2, 4, 3, 8, dtype=torch.float64); b = torch.randn(4, dtype=torch.float64)
     dy = torch.randn_like(x); ddx = torch.randn_like(x)
 
