@@ -867,6 +867,17 @@ def test_layout_transposes(cno, shape, dtype):
     assert torch.equal(y.permute(0, 2, 3, 1).contiguous(), x.permute(0, 2, 3, 1).contiguous())      # the bytes, not only the logical view
     z = layout.to_nchw(y)
     assert z.is_contiguous() and torch.equal(z, x)
+    if x.numel():
+        # straight through the C ABI into a buffer with guard zones: nothing may be written outside the tensor
+        from pregenerating_pde_b200.torch_utils.custom_ops import _ptr, _stream
+        lib, pad = cno._lib.load(), 256
+        n, c, h, w = shape
+        for fn in (lib.cno_nchw_to_nhwc, lib.cno_nhwc_to_nchw):
+            buf = torch.full((x.numel() + 2 * pad,), 7.0, device=DEV, dtype=dtype)
+            out = buf[pad:pad + x.numel()]
+            assert fn(_ptr(x), _ptr(out), {torch.float32: 0, torch.bfloat16: 1}[dtype], n, c, h * w, _stream(x)) == 0
+            torch.cuda.synchronize()
+            assert bool((buf[:pad] == 7.0).all()) and bool((buf[pad + x.numel():] == 7.0).all())
 
 
 @pytest.mark.gpu

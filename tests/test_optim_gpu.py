@@ -66,11 +66,23 @@ def test_unaligned_views_and_flat_gradients(cno):
         a = torch.nn.Parameter(flat_p[o:o + n].clone()); b = torch.nn.Parameter(flat_p[o:o + n].clone())
         a.grad = flat_g[o:o + n]; b.grad = flat_g[o:o + n].clone()
         pa.append(a); pb.append(b); o += n
+    # parameters of the kernel-driven optimiser live inside one guarded buffer: the update must not touch a float outside them
+    guard = torch.full((sum(sizes) + 64 * (len(sizes) + 1),), 3.0, device=DEV)
+    o = 64
+    for a, n in zip(pa, sizes):
+        guard[o:o + n] = a.data
+        a.data = guard[o:o + n]
+        o += n + 64
     oa, ob = MultiTensorAdamW(pa, lr=1e-2), torch.optim.AdamW(pb, lr=1e-2)
     for _ in range(3):
         oa.step(); ob.step()
     for a, b in zip(pa, pb):
         assert rel(a.detach(), b.detach()) < 2e-6
+    o = 0
+    for n in sizes:
+        assert bool((guard[o:o + 64] == 3.0).all())
+        o += 64 + n
+    assert bool((guard[o:] == 3.0).all())
 
 
 def test_graph_captured_step_replays(cno):
