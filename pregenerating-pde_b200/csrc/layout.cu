@@ -29,6 +29,38 @@ __global__ void __launch_bounds__(256) transpose_kernel(const T* __restrict__ in
             if (r0 + i < R && s0 + j < S) out[(size_t)(s0 + j) * R + r0 + i] = tile[i][j];
 }
 
+// 16-bit elements: a thread moves 2 x 2 blocks - two 32-bit loads (two consecutive source rows, two consecutive columns each), two
+// byte permutes, two 32-bit stores - so both sides move 128 bytes per warp request like the fp32 kernel (the element-wise version
+// moves 64).  Tile: 64 x 64 elements; needs even R and S (rows stay 4-byte aligned).
+__global__ void __launch_bounds__(256) transpose16_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int R, int S) {
+    __shared__ uint32_t even[32][33], odd[32][33];        // [source column pair][source row pair]: columns 2j / 2j + 1 of the tile
+    const size_t plane = (size_t)R * S / 2;                // in 32-bit words
+    in += blockIdx.z * plane; out += blockIdx.z * plane;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int s0 = blockIdx.x * 64, r0 = blockIdx.y * 64, Sw = S >> 1, Rw = R >> 1;
+    uint32_t a[4], b[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int rp = ty + 8 * k, r = r0 + 2 * rp, sw = (s0 >> 1) + tx;
+        const bool ok = r < R && sw < Sw;                  // R even: r < R implies r + 1 < R
+        a[k] = ok ? in[(size_t)r * Sw + sw] : 0u;
+        b[k] = ok ? in[(size_t)(r + 1) * Sw + sw] : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int rp = ty + 8 * k;
+        even[tx][rp] = __byte_perm(a[k], b[k], 0x5410);   // column 2 tx:     rows 2 rp, 2 rp + 1
+        odd[tx][rp] = __byte_perm(a[k], b[k], 0x7632);    // column 2 tx + 1
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const int sl = ty + 8 * k;                         // output row (source column) within the tile, 0 .. 63
+        const int sg = s0 + sl, rw = (r0 >> 1) + tx;
+        if (sg < S && rw < Rw) out[(size_t)sg * Rw + rw] = (sl & 1) ? odd[sl >> 1][tx] : even[sl >> 1][tx];
+    }
+}
+
 template <class T, int TS, int TR> int launch_tile(const T* in, T* out, int n, int R, int S, cudaStream_t st) {
     dim3 grid((unsigned)((S + TS - 1) / TS), (unsigned)((R + TR - 1) / TR), (unsigned)n);
     transpose_kernel<T, TS, TR><<<grid, 256, 0, st>>>(in, out, R, S);
@@ -49,7 +81,14 @@ int dispatch(const void* in, void* out, int dtype, int n, int R, int S, void* st
     if (n == 0) return 0;
     switch (dtype) {
         case CNO_F32: return launch<float>(in, out, n, R, S, (cudaStream_t)stream);
-        case CNO_BF16: case CNO_F16: return launch<uint16_t>(in, out, n, R, S, (cudaStream_t)stream);
+        case CNO_BF16: case CNO_F16:
+            if (!(R & 1) && !(S & 1) && !(((uintptr_t)in | (uintptr_t)out) & 3u) && (R + 63) / 64 <= 65535) {
+                dim3 grid((unsigned)((S + 63) / 64), (unsigned)((R + 63) / 64), (unsigned)n);
+                transpose16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(static_cast<const uint32_t*>(in), static_cast<uint32_t*>(out), R, S);
+                CNO_LAUNCH_CHECK();
+                return 0;
+            }
+            return launch<uint16_t>(in, out, n, R, S, (cudaStream_t)stream);
     }
     cno_set_error("layout: unsupported dtype %d", dtype);
     return (int)cudaErrorInvalidValue;

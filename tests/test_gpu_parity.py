@@ -855,7 +855,8 @@ def test_two_devices_one_process(cno):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
-@pytest.mark.parametrize('shape', [(2, 7, 16, 16), (3, 32, 33, 17), (1, 5, 8, 8), (2, 64, 128, 128), (1, 256, 8, 8), (2, 33, 1, 40), (0, 4, 8, 8)])
+@pytest.mark.parametrize('shape', [(2, 7, 16, 16), (3, 32, 33, 17), (1, 5, 8, 8), (2, 64, 128, 128), (1, 256, 8, 8), (2, 33, 1, 40), (0, 4, 8, 8),
+                                   (2, 6, 10, 10), (1, 34, 6, 7), (3, 130, 9, 14), (2, 128, 64, 64)])
 def test_layout_transposes(cno, shape, dtype):
     """cno_nchw_to_nhwc / cno_nhwc_to_nchw (csrc/layout.cu): bit-exact against torch's memory-format copies, ragged sizes included"""
     from pregenerating_pde_b200 import layout

@@ -1,5 +1,5 @@
 """torch.profiler (CUPTI) timeline of the CNO training step: real (warm, overlapped) kernel durations by name + GPU busy time.
-usage: python tools/prof_train_torch.py [graph 0|1] [batch]"""
+usage: python tools/prof_train_torch.py [graph 0|1] [batch] [train|finetune] [fp32|bf16]"""
 import os, sys, collections, re
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -8,8 +8,15 @@ from torch.profiler import profile, ProfilerActivity
 graph = int(sys.argv[1]) if len(sys.argv) > 1 else 1
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 32
 torch.backends.cudnn.benchmark = True
-tr = cno.train.Trainer(device='cuda', graph=bool(graph))
-b = cno.train.synthetic_fpo_batch(B, device='cuda')
+mode = sys.argv[3] if len(sys.argv) > 3 else 'train'
+ac = torch.bfloat16 if (len(sys.argv) > 4 and sys.argv[4] == 'bf16') else None
+if mode == 'finetune':
+    ft = cno.finetune.wide_finetune_config()
+    tr = cno.train.Trainer(device='cuda', graph=bool(graph), mode='finetune', ft=ft, autocast=ac)
+    b = cno.train.synthetic_finetune_batch(B, ft, device='cuda')
+else:
+    tr = cno.train.Trainer(device='cuda', graph=bool(graph), autocast=ac)
+    b = cno.train.synthetic_fpo_batch(B, device='cuda')
 for _ in range(5): tr.step(*b)
 torch.cuda.synchronize()
 with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
