@@ -29,28 +29,38 @@ __global__ void __launch_bounds__(256) transpose_kernel(const T* __restrict__ in
             if (r0 + i < R && s0 + j < S) out[(size_t)(s0 + j) * R + r0 + i] = tile[i][j];
 }
 
-// 16-bit elements: a thread moves 2 x 2 blocks - two 32-bit loads (two consecutive source rows, two consecutive columns each), two
-// byte permutes, two 32-bit stores - so both sides move 128 bytes per warp request like the fp32 kernel (the element-wise version
-// moves 64).  Tile: 64 x 64 elements; needs even R and S (rows stay 4-byte aligned).
-__global__ void __launch_bounds__(256) transpose16_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int R, int S) {
-    __shared__ uint32_t even[32][33], odd[32][33];        // [source column pair][source row pair]: columns 2j / 2j + 1 of the tile
-    const size_t plane = (size_t)R * S / 2;                // in 32-bit words
+// 2 x 2 blocks per thread: two loads of two consecutive columns from two consecutive source rows, a re-pairing, two stores of two
+// consecutive destination columns - 32-bit accesses for 16-bit elements (128 bytes per warp request instead of 64), 64-bit accesses for
+// 32-bit elements.  Tile: 64 x 64 elements; needs even R and S and word-aligned pointers.
+template <class W> struct Pair;
+template <> struct Pair<uint32_t> {                        // two 16-bit elements per word
+    static __device__ __forceinline__ uint32_t lo(uint32_t a, uint32_t b) { return __byte_perm(a, b, 0x5410); }
+    static __device__ __forceinline__ uint32_t hi(uint32_t a, uint32_t b) { return __byte_perm(a, b, 0x7632); }
+};
+template <> struct Pair<uint2> {                           // two 32-bit elements per word
+    static __device__ __forceinline__ uint2 lo(uint2 a, uint2 b) { return make_uint2(a.x, b.x); }
+    static __device__ __forceinline__ uint2 hi(uint2 a, uint2 b) { return make_uint2(a.y, b.y); }
+};
+template <class W>
+__global__ void __launch_bounds__(256) transpose2x2_kernel(const W* __restrict__ in, W* __restrict__ out, int R, int S) {
+    __shared__ W even[32][33], odd[32][33];                // [source column pair][source row pair]: columns 2j / 2j + 1 of the tile
+    const size_t plane = (size_t)R * S / 2;                // in words of two elements
     in += blockIdx.z * plane; out += blockIdx.z * plane;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int s0 = blockIdx.x * 64, r0 = blockIdx.y * 64, Sw = S >> 1, Rw = R >> 1;
-    uint32_t a[4], b[4];
+    W a[4], b[4];
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         const int rp = ty + 8 * k, r = r0 + 2 * rp, sw = (s0 >> 1) + tx;
         const bool ok = r < R && sw < Sw;                  // R even: r < R implies r + 1 < R
-        a[k] = ok ? in[(size_t)r * Sw + sw] : 0u;
-        b[k] = ok ? in[(size_t)(r + 1) * Sw + sw] : 0u;
+        a[k] = ok ? in[(size_t)r * Sw + sw] : W{};
+        b[k] = ok ? in[(size_t)(r + 1) * Sw + sw] : W{};
     }
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         const int rp = ty + 8 * k;
-        even[tx][rp] = __byte_perm(a[k], b[k], 0x5410);   // column 2 tx:     rows 2 rp, 2 rp + 1
-        odd[tx][rp] = __byte_perm(a[k], b[k], 0x7632);    // column 2 tx + 1
+        even[tx][rp] = Pair<W>::lo(a[k], b[k]);            // column 2 tx:     rows 2 rp, 2 rp + 1
+        odd[tx][rp] = Pair<W>::hi(a[k], b[k]);             // column 2 tx + 1
     }
     __syncthreads();
 #pragma unroll
@@ -59,6 +69,13 @@ __global__ void __launch_bounds__(256) transpose16_kernel(const uint32_t* __rest
         const int sg = s0 + sl, rw = (r0 >> 1) + tx;
         if (sg < S && rw < Rw) out[(size_t)sg * Rw + rw] = (sl & 1) ? odd[sl >> 1][tx] : even[sl >> 1][tx];
     }
+}
+
+template <class W> int launch2x2(const void* in, void* out, int n, int R, int S, cudaStream_t st) {
+    dim3 grid((unsigned)((S + 63) / 64), (unsigned)((R + 63) / 64), (unsigned)n);
+    transpose2x2_kernel<W><<<grid, 256, 0, st>>>(static_cast<const W*>(in), static_cast<W*>(out), R, S);
+    CNO_LAUNCH_CHECK();
+    return 0;
 }
 
 template <class T, int TS, int TR> int launch_tile(const T* in, T* out, int n, int R, int S, cudaStream_t st) {
@@ -79,15 +96,15 @@ int dispatch(const void* in, void* out, int dtype, int n, int R, int S, void* st
     CNO_CHECK_ARG(in && out, "layout: null pointer");
     CNO_CHECK_ARG(n >= 0 && R > 0 && S > 0 && n <= 65535 && (R + 31) / 32 <= 65535, "layout: bad sizes n=%d %d x %d", n, R, S);
     if (n == 0) return 0;
+    static EnvFlag env_f32_2x2;
+    const bool even = !(R & 1) && !(S & 1) && (R + 63) / 64 <= 65535;
+    const bool use2x2_f32 = env_f32_2x2.on("CNO_LAYOUT_F32_2X2");
     switch (dtype) {
-        case CNO_F32: return launch<float>(in, out, n, R, S, (cudaStream_t)stream);
+        case CNO_F32:
+            if (even && !(((uintptr_t)in | (uintptr_t)out) & 7u) && use2x2_f32) return launch2x2<uint2>(in, out, n, R, S, (cudaStream_t)stream);
+            return launch<float>(in, out, n, R, S, (cudaStream_t)stream);
         case CNO_BF16: case CNO_F16:
-            if (!(R & 1) && !(S & 1) && !(((uintptr_t)in | (uintptr_t)out) & 3u) && (R + 63) / 64 <= 65535) {
-                dim3 grid((unsigned)((S + 63) / 64), (unsigned)((R + 63) / 64), (unsigned)n);
-                transpose16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(static_cast<const uint32_t*>(in), static_cast<uint32_t*>(out), R, S);
-                CNO_LAUNCH_CHECK();
-                return 0;
-            }
+            if (even && !(((uintptr_t)in | (uintptr_t)out) & 3u)) return launch2x2<uint32_t>(in, out, n, R, S, (cudaStream_t)stream);
             return launch<uint16_t>(in, out, n, R, S, (cudaStream_t)stream);
     }
     cno_set_error("layout: unsupported dtype %d", dtype);
