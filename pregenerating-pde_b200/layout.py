@@ -45,8 +45,9 @@ class _Conv2dNHWC(torch.autograd.Function):
         ctx.param_dtypes = (weight.dtype, None if bias is None else bias.dtype)
         ctx.weight_stride, ctx.weight_contiguous = weight.stride(), weight.is_contiguous()
         if cast is not None:                             # autocast: parameters are cast HERE so that their gradients are cast back on the side stream
-            weight, bias = weight.to(cast), (None if bias is None else bias.to(cast))
-        w_cl = weight.contiguous(memory_format=torch.channels_last)          # once per step; forward, data and weight gradient all use it
+            bias = None if bias is None else bias.to(cast)
+        # once per step, cast and layout in one copy; forward, data gradient and weight gradient all use it
+        w_cl = weight.to(dtype=cast if cast is not None else weight.dtype, memory_format=torch.channels_last)
         y_cl = torch.nn.functional.conv2d(x_cl, w_cl, bias, stride, padding, dilation, groups)
         ctx.save_for_backward(x_cl, w_cl)
         ctx.cfg = (stride, padding, dilation, groups, None if bias is None else list(bias.shape))
@@ -76,9 +77,9 @@ class _Conv2dNHWC(torch.autograd.Function):
             with (torch.cuda.stream(side) if side is not None else contextlib.nullcontext()):
                 _, dw, db = torch.ops.aten.convolution_backward(dy_cl, x_cl, w_cl, bias_sizes, *args, [False, ctx.needs_input_grad[1], want_b])
                 if dw is not None:                       # in the layout of the parameter (channels_last weights get their gradient as cuDNN wrote it)
-                    dw = dw.to(ctx.param_dtypes[0])
-                    if any(sa != sb for n, sa, sb in zip(dw.shape, dw.stride(), ctx.weight_stride) if n > 1):
-                        dw = dw.contiguous() if ctx.weight_contiguous else dw.contiguous(memory_format=torch.channels_last)
+                    if dw.dtype != ctx.param_dtypes[0] or any(sa != sb for n, sa, sb in zip(dw.shape, dw.stride(), ctx.weight_stride) if n > 1):
+                        dw = dw.to(dtype=ctx.param_dtypes[0],            # cast and layout in one copy
+                                   memory_format=torch.contiguous_format if ctx.weight_contiguous else torch.channels_last)
                 if db is not None:
                     db = db.to(ctx.param_dtypes[1])
                 # dw / db are NOT put on the keep-alive list: autograd must be able to adopt them as .grad without a copy (a second
