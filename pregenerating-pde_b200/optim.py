@@ -19,7 +19,14 @@ assert _RECORD.itemsize == 56
 
 def _dense(t):
     """every element of the storage range exactly once (contiguous in some dimension order)"""
-    return t.is_contiguous() or (t.ndim == 4 and t.is_contiguous(memory_format=torch.channels_last)) or t.is_non_overlapping_and_dense()
+    if t.is_contiguous():
+        return True
+    expect = 1
+    for n, st in sorted(((n, st) for n, st in zip(t.shape, t.stride()) if n > 1), key=lambda v: v[1]):
+        if st != expect:
+            return False
+        expect *= n
+    return True
 
 
 def _same_layout(a, b):

@@ -164,3 +164,36 @@ def test_missing_library_is_a_hard_error(pkg, monkeypatch):
     monkeypatch.setattr(pkg._lib, 'LIB_PATH', '/nonexistent/libcno_b200.so')
     with pytest.raises(pkg._lib.CnoError):
         pkg.custom_ops.get_plugin('filtered_lrelu_plugin')
+
+
+def test_adam_table_record_matches_the_c_struct(pkg, tmp_path):
+    """optim.MultiTensorAdamW uploads numpy records that cno_adamw_multi reads as CnoAdamTensor (include/cno_b200.h): same size, same
+    field offsets as the C compiler lays the struct out"""
+    import shutil, subprocess
+    from pregenerating_pde_b200 import optim
+    cc = shutil.which('gcc') or shutil.which('cc')
+    if cc is None:
+        pytest.skip('no C compiler')
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / 'off.c'
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "cno_b200.h"\nint main(void) { printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", '
+                   'sizeof(CnoAdamTensor), offsetof(CnoAdamTensor, param), offsetof(CnoAdamTensor, grad), offsetof(CnoAdamTensor, exp_avg), '
+                   'offsetof(CnoAdamTensor, exp_avg_sq), offsetof(CnoAdamTensor, numel), offsetof(CnoAdamTensor, lr), '
+                   'offsetof(CnoAdamTensor, weight_decay), offsetof(CnoAdamTensor, first_chunk), offsetof(CnoAdamTensor, pad)); return 0; }\n')
+    exe = tmp_path / 'off'
+    subprocess.check_call([cc, '-I', os.path.join(root, 'include'), str(src), '-o', str(exe)])
+    got = [int(v) for v in subprocess.check_output([str(exe)]).split()]
+    rec = optim._RECORD
+    want = [rec.itemsize] + [rec.fields[n][1] for n in ('param', 'grad', 'exp_avg', 'exp_avg_sq', 'numel', 'lr', 'weight_decay', 'first_chunk', 'pad')]
+    assert got == want
+
+
+def test_optimiser_layout_helpers():
+    from pregenerating_pde_b200 import optim
+    a = torch.zeros(8, 4, 3, 3)
+    cl = a.contiguous(memory_format=torch.channels_last)
+    assert optim._dense(a) and optim._dense(cl) and not optim._dense(a[:, ::2])
+    assert optim._same_layout(cl, torch.ones(8, 4, 3, 3).contiguous(memory_format=torch.channels_last))
+    assert not optim._same_layout(cl, a)
+    # size-1 dimensions carry arbitrary strides: they must not make equal layouts look different
+    assert optim._same_layout(torch.zeros(4, 1, 3, 3), torch.zeros(4, 1, 3, 3).contiguous(memory_format=torch.channels_last))
