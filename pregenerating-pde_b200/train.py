@@ -4,6 +4,8 @@ forward + relative-L1 loss + backward + AdamW, one process per GPU with torch DD
 the only exchange), optional whole-step CUDA-graph capture on a single GPU.
 """
 import math
+import contextlib
+import os
 import torch
 import torch.distributed as dist
 from torch import nn
@@ -88,6 +90,9 @@ def freeze_dead_parameters(model):
     return n
 
 
+GATHER_ON_SIDE_STREAM = os.environ.get('CNO_GATHER_ON_SIDE_STREAM', '1') == '1'
+
+
 class Trainer:
     """One optimisation step = forward, relative L1 (CNO_timeModule_CIN.py:939), backward, (all-reduce), AdamW (:996).
 
@@ -170,21 +175,32 @@ class Trainer:
     def _launch_bucket(self, b):
         start, end, members = self.buckets[b]
         self._launched[b] = True
-        if self._side is not None:
-            self._side.join_param_grad_stream()
         have = [p for p in members if p.grad is not None]
-        if len(have) < len(members):                   # a parameter without a gradient this step contributes zeros
-            self.flat_grad[start:end].zero_()
-        if have:
-            torch._foreach_copy_([self._views[p] for p in have], [p.grad for p in have])
+        side = self._side.PARAM_GRAD_STREAM if (self._side is not None and self.comm_stream is not None and GATHER_ON_SIDE_STREAM) else None
+        if side is None and self._side is not None:
+            self._side.join_param_grad_stream()
+        cur = torch.cuda.current_stream(self.device) if self.comm_stream is not None else None
+        if side is not None:
+            # Most gradients of a bucket (convolution weights, FILM parameters) are produced on the parameter-gradient side stream.  The
+            # gather runs THERE, behind them, so the compute stream never waits for weight gradients in the middle of backward; the few
+            # gradients produced on the compute stream are covered by the wait below and handed over with record_stream.
+            side.wait_stream(cur)
+        with (torch.cuda.stream(side) if side is not None else contextlib.nullcontext()):
+            if len(have) < len(members):               # a parameter without a gradient this step contributes zeros
+                self.flat_grad[start:end].zero_()
+            if have:
+                grads = [p.grad for p in have]
+                torch._foreach_copy_([self._views[p] for p in have], grads)
+                if side is not None:
+                    for g in grads:
+                        g.record_stream(side)
         for p in members:
             p.grad = self._views[p]
         if self.comm_stream is None:                   # CPU / gloo: same arithmetic, no overlap
             dist.all_reduce(self.flat_grad[start:end])
             self.flat_grad[start:end].mul_(1.0 / self.world)
             return
-        cur = torch.cuda.current_stream(self.device)
-        self.comm_stream.wait_stream(cur)              # the bucket is complete on the compute stream
+        self.comm_stream.wait_stream(side if side is not None else cur)      # the bucket is complete on that stream
         with torch.cuda.stream(self.comm_stream):
             dist.all_reduce(self.flat_grad[start:end], op=dist.ReduceOp.AVG)
 

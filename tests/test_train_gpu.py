@@ -104,3 +104,14 @@ def test_rollout_graph_equals_eager(cno):
         g.replay()
     torch.cuda.synchronize()
     assert torch.equal(out, ref)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs')
+def test_multi_rank_gradients_side_stream_gather(cno):
+    """torchrun, 2 ranks over NCCL: reduced gradients with the bucket gather on the parameter-gradient side stream equal those with the
+    gather on the compute stream, eager and captured, and are identical on every rank (tools/check_ddp_gather.py)"""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr', '127.0.0.1',
+                          '--master-port', '29541', os.path.join(root, 'tools', 'check_ddp_gather.py')], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and 'OK, worst relative gradient difference' in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
